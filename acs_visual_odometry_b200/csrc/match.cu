@@ -1,0 +1,130 @@
+// match.cu — K4: brute-force Hamming 2-NN matcher with Lowe ratio test.
+//
+// Replaces matchCustomBinaryDescriptorsThreadPool + hammingDistance
+// (feature_matching_parallel/feature_matching_parallel.cpp:39-113).  Two distance definitions:
+//   REF32   the reference thread-pool matcher popcounts only the first 32 descriptor bytes, i.e. tests
+//           0..31 (:39-47) -> word 0 of the packed descriptor;
+//   FULL512 all 512 tests (matching_serial.cpp:24-40) -> all 16 words.
+// Per query the reference keeps the two smallest distances of the multiset and the FIRST index that
+// attains the minimum (:82-92).  Both follow from the two smallest packed keys (dist << 16 | index):
+// keys are unique, their order is (dist, index) lexicographic, so min1 carries (d1, first index) and
+// min2's distance is the second smallest of the multiset.
+//
+//   k_match     grid (query tiles, VO_MATCH_SPLITS train slices, pairs).  One query per thread, query
+//               words register-resident; train descriptors staged in shared memory and read with
+//               broadcast loads; XOR + POPC on the integer pipe; partial (min1, min2) per slice.
+//   k_finalize  one CTA per pair: merges the slices, applies `float(d1) < ratio * float(d2)` in fp32
+//               (:95-97) and compacts accepted (query, train) pairs in query order with a block scan.
+#include "vo_internal.cuh"
+
+namespace {
+
+constexpr int MT_NT = 128;    // queries per CTA
+constexpr int MT_TILE = 128;  // train descriptors per shared-memory tile
+
+__device__ __forceinline__ void push_key(uint32_t key, uint32_t& m1, uint32_t& m2) {
+    m2 = min(m2, max(m1, key));
+    m1 = min(m1, key);
+}
+
+template <int WORDS>
+__global__ void __launch_bounds__(MT_NT) k_match(const MatchArgs a) {
+    __shared__ __align__(16) uint32_t s_t[MT_TILE * WORDS];
+    const int pair = blockIdx.z, split = blockIdx.y;
+    const int qs = a.qslot[pair], ts = a.tslot[pair];
+    const int n1 = a.nkp[qs], n2 = a.nkp[ts];
+    if ((int)blockIdx.x * MT_NT >= n1) return;
+    const int qi = blockIdx.x * MT_NT + threadIdx.x;
+    const uint32_t* __restrict__ qd = a.desc + (size_t)qs * a.kp_stride * 16;
+    const uint32_t* __restrict__ td = a.desc + (size_t)ts * a.kp_stride * 16;
+
+    uint32_t q[WORDS];
+#pragma unroll
+    for (int w = 0; w < WORDS; ++w) q[w] = qi < n1 ? qd[(size_t)qi * 16 + w] : 0u;
+
+    const int chunk = (n2 + VO_MATCH_SPLITS - 1) / VO_MATCH_SPLITS;
+    const int j_begin = split * chunk, j_end = min(n2, j_begin + chunk);
+    uint32_t m1 = 0xFFFFFFFFu, m2 = 0xFFFFFFFFu;
+    for (int j0 = j_begin; j0 < j_end; j0 += MT_TILE) {
+        const int cnt = min(MT_TILE, j_end - j0);
+        __syncthreads();
+        for (int idx = threadIdx.x; idx < cnt * WORDS; idx += MT_NT) {
+            const int r = idx / WORDS, w = idx - r * WORDS;
+            s_t[idx] = td[(size_t)(j0 + r) * 16 + w];
+        }
+        __syncthreads();
+        for (int r = 0; r < cnt; ++r) {
+            int d = 0;
+#pragma unroll
+            for (int w = 0; w < WORDS; ++w) d += __popc(q[w] ^ s_t[r * WORDS + w]);
+            push_key(((uint32_t)d << 16) | (uint32_t)(j0 + r), m1, m2);
+        }
+    }
+    if (qi < n1) a.partial[((size_t)pair * VO_MATCH_SPLITS + split) * a.max_kp + qi] = make_uint2(m1, m2);
+}
+
+constexpr int FN_NT = 1024;
+
+__global__ void __launch_bounds__(FN_NT) k_finalize(const MatchArgs a) {
+    __shared__ int s_warp[FN_NT / 32];
+    __shared__ int s_base;
+    const int pair = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int n1 = a.nkp[a.qslot[pair]], n2 = a.nkp[a.tslot[pair]];
+    int2* __restrict__ out = a.pairs + (size_t)pair * a.max_kp;
+    int* __restrict__ raw = a.raw + (size_t)pair * a.max_kp * 3;
+    if (tid == 0) s_base = 0;
+    __syncthreads();
+    for (int q0 = 0; q0 < n1; q0 += FN_NT) {
+        const int qi = q0 + tid;
+        bool accept = false;
+        int best_idx = -1;
+        if (qi < n1) {
+            uint32_t m1 = 0xFFFFFFFFu, m2 = 0xFFFFFFFFu;
+            if (n2 > 0) {
+#pragma unroll
+                for (int s = 0; s < VO_MATCH_SPLITS; ++s) {
+                    const uint2 p = a.partial[((size_t)pair * VO_MATCH_SPLITS + s) * a.max_kp + qi];
+                    push_key(p.x, m1, m2);
+                    push_key(p.y, m1, m2);
+                }
+            }
+            const bool has1 = m1 != 0xFFFFFFFFu, has2 = m2 != 0xFFFFFFFFu;
+            const int d1 = has1 ? (int)(m1 >> 16) : 0x7FFFFFFF, d2 = has2 ? (int)(m2 >> 16) : 0x7FFFFFFF;
+            best_idx = has1 ? (int)(m1 & 0xFFFFu) : -1;
+            raw[(size_t)qi * 3 + 0] = d1; raw[(size_t)qi * 3 + 1] = best_idx; raw[(size_t)qi * 3 + 2] = d2;
+            // bestIdx != -1 && secondBestIdx != -1 && bestDist < ratioThreshold * secondBestDist   (int < float*int)
+            accept = has1 && has2 && ((float)d1 < __fmul_rn(a.ratio, (float)d2));
+        }
+        const unsigned bal = __ballot_sync(0xFFFFFFFFu, accept);
+        if (lane == 0) s_warp[warp] = __popc(bal);
+        __syncthreads();
+        int before = 0, total = 0;
+        for (int w = 0; w < FN_NT / 32; ++w) {
+            const int c = s_warp[w];
+            before += w < warp ? c : 0;
+            total += c;
+        }
+        const int base = s_base;
+        if (accept) out[base + before + __popc(bal & ((1u << lane) - 1u))] = make_int2(qi, best_idx);
+        __syncthreads();
+        if (tid == 0) s_base = base + total;
+        __syncthreads();
+    }
+    if (tid == 0) a.nmatch[pair] = s_base;
+}
+
+}  // namespace
+
+cudaError_t launch_match(const MatchArgs& a, int n_pairs, int max_n1, cudaStream_t st) {
+    if (n_pairs <= 0 || max_n1 <= 0) return cudaSuccess;
+    const dim3 grid((max_n1 + MT_NT - 1) / MT_NT, VO_MATCH_SPLITS, n_pairs);
+    if (a.match_bits == VO_MATCH_REF32) k_match<1><<<grid, MT_NT, 0, st>>>(a);
+    else k_match<16><<<grid, MT_NT, 0, st>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_match_finalize(const MatchArgs& a, int n_pairs, cudaStream_t st) {
+    if (n_pairs <= 0) return cudaSuccess;
+    k_finalize<<<n_pairs, FN_NT, 0, st>>>(a);
+    return cudaGetLastError();
+}

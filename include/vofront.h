@@ -1,0 +1,171 @@
+/* vofront.h — C ABI of libvofront.so: the B200-native feature front-end
+ * (7x7 Gaussian blur -> gradients -> 5x5 structure tensor -> Shi-Tomasi response -> NMS/top-N ->
+ * FREAK-style 512-test descriptors -> brute-force Hamming 2-NN ratio matching).
+ *
+ * This is the drop-in boundary for the hot path of Bohdanok/ACS_Visual_Odometry.  Every entry
+ * point names the reference interface it replaces (paths relative to the reference root).
+ * Plain pointers and sizes only; no C++ or torch types cross it.  All work is done by hand-written
+ * sm_100a CUDA kernels; there is no CPU fallback: without a CUDA device vo_create() fails.
+ *
+ * Conventions
+ *   - every function returning int returns VO_OK (0) or a negative VO_ERR_* code;
+ *     vo_last_error(ctx) gives a human-readable message for the last failure on that context
+ *     (ctx == NULL: last vo_create() failure on this thread).  Nothing throws across the ABI.
+ *   - a vo_ctx belongs to one GPU; it is not thread-safe, independent contexts are fully concurrent.
+ *   - images are 8-bit grayscale, row-major, `pitch` bytes between rows (pitch >= cols).
+ *   - keypoints are (x = column, y = row) float pairs, sorted by (y, x) ascending, exactly the order
+ *     of the reference (feature_extraction_parallel/feature_extraction_parallel.cpp:276-282); match
+ *     indices refer to that order.
+ *   - descriptors: "desc512" = n x 512 bytes, one byte (0/1) per test, the reference's layout
+ *     (feature_extraction_parallel.cpp:324); "packed" = n x 16 little-endian uint32 words,
+ *     bit (j & 31) of word (j >> 5) = test j.
+ */
+#ifndef VOFRONT_H
+#define VOFRONT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VO_OK 0
+#define VO_ERR_BAD_ARG (-1)   /* null pointer, size out of range, slot out of range, bad descriptor bytes */
+#define VO_ERR_CUDA (-2)      /* a CUDA runtime call or kernel failed; see vo_last_error */
+#define VO_ERR_CAPACITY (-3)  /* NMS candidates or matches exceeded a buffer; never truncated silently */
+#define VO_ERR_NO_DEVICE (-4) /* no usable sm_100 device */
+#define VO_ERR_STATE (-5)     /* slot holds no frame / sequence not uploaded */
+
+#define VO_MATCH_REF32 32     /* hammingDistance of feature_matching_parallel/feature_matching_parallel.cpp:39-47:
+                                 only the first 32 tests are compared (what VisualOdometry runs) */
+#define VO_MATCH_FULL512 512  /* all 512 tests, matching_serial.cpp:24-40 */
+
+#define VO_PRESET_CPU_REF 0    /* thread-pool path: threshold 25000 (corner_detection_parallel.h:16),
+                                  NMS 5, top-N 1500 (feature_extraction_parallel.cpp:274) */
+#define VO_PRESET_VO_GPU_REF 1 /* the variant VisualOdometry links: threshold 20000
+                                  (corner_detection_parallel_GPU.h:25), NMS 3, top-N 2000
+                                  (feature_extraction_parallel_GPU.cpp:235) */
+
+#define VO_DBG_BLURRED 1  /* rows x cols uint8, tightly packed */
+#define VO_DBG_RESPONSE 2 /* rows x cols float (thresholded R_array), tightly packed */
+#define VO_DBG_ANGLES 3   /* n float, FREAK orientation per keypoint */
+
+typedef struct vo_ctx vo_ctx;
+
+/* The literals the reference scatters over globals, constexprs and call sites. */
+typedef struct vo_params {
+    float threshold;   /* RESPONSE_THRESHOLD: responses <= threshold become 0 */
+    int nms_window;    /* k of non_maximum_suppression (odd, 3..9) */
+    int max_keypoints; /* N of non_maximum_suppression; <= the context's max_keypoints */
+    float ratio;       /* Lowe ratio, 0.75f at every reference call site */
+    int match_bits;    /* VO_MATCH_REF32 or VO_MATCH_FULL512 */
+} vo_params;
+
+int vo_params_preset(vo_params* p, int preset);
+
+/* ---- context --------------------------------------------------------------------------------
+ * Replaces the per-process state of the reference: `thread_pool` (feature_extraction_parallel/
+ * threadpool.h:15) and `GPU_settings{cl::Program, cl::Device, cl::Context}`
+ * (feature_extraction_parallel_GPU/corner_detection_parallel_GPU.h:48-52, built in
+ * VisualOdometry.cpp:14-23).  All device buffers are sized here; nothing is allocated per frame.
+ * n_slots = number of device-resident frame records (image, blurred image, response, candidates,
+ * keypoints, packed descriptors); batched calls use consecutive slots modulo n_slots. */
+int vo_create(vo_ctx** out, int device, int max_rows, int max_cols, int max_keypoints, int n_slots);
+void vo_destroy(vo_ctx* ctx);
+const char* vo_last_error(const vo_ctx* ctx);
+int vo_device_count(void);
+int vo_sync(vo_ctx* ctx);
+
+/* Pinned host memory for callers that want truly asynchronous copies (optional). */
+void* vo_host_alloc(size_t bytes);
+void vo_host_free(void* p);
+
+/* ---- extraction --------------------------------------------------------------------------------
+ * Replaces feature_extraction_manager_with_points
+ *   (cv::Mat&, thread_pool&)            feature_extraction_parallel/feature_extraction_parallel.cpp:215
+ *   (const cv::Mat&, const GPU_settings&) feature_extraction_parallel_GPU/feature_extraction_parallel_GPU.cpp:194
+ * i.e. GaussianBlur 7x7 -> direction_gradients_worker -> shitomasi_corner_detection_worker ->
+ * non_maximum_suppression -> sort -> FREAK_feature_description_worker.  The result stays on the device
+ * in `slot`; fetch it with vo_frame_fetch and/or match it with vo_match. */
+int vo_extract(vo_ctx* ctx, const uint8_t* gray, int rows, int cols, size_t pitch, const vo_params* p, int slot);
+/* Same, from an interleaved 8-bit BGR image (custom_bgr2gray, corner_detection_parallel.cpp:14-28). */
+int vo_extract_bgr(vo_ctx* ctx, const uint8_t* bgr, int rows, int cols, size_t pitch, const vo_params* p, int slot);
+/* n frames, `frame_stride` bytes apart, into slots first_slot .. first_slot+n-1 (mod n_slots), one launch
+ * per stage for the whole batch. n <= n_slots. */
+int vo_extract_batch(vo_ctx* ctx, const uint8_t* gray, int n, int rows, int cols, size_t pitch, size_t frame_stride,
+                     const vo_params* p, int first_slot);
+
+/* Copy a slot's results to the host.  Any output pointer may be NULL.  *n receives the keypoint count;
+ * kp_xy needs 2*n floats, desc512 512*n bytes, desc_packed 16*n words (size them with max_keypoints). */
+int vo_frame_fetch(vo_ctx* ctx, int slot, int* n, float* kp_xy, uint8_t* desc512, uint32_t* desc_packed);
+/* Stage probes for parity tests (VO_DBG_*): the blurred image / response map / angles of the frame that
+ * was last extracted into `slot`. */
+int vo_debug_fetch(vo_ctx* ctx, int slot, int what, void* dst);
+
+/* Stage entry points mirroring the reference's public statics, host buffers in and out:
+ *   vo_blur       cv::GaussianBlur(src, dst, Size(7,7), 0)               feature_extraction_parallel.cpp:223
+ *   vo_response   direction_gradients_worker + shitomasi_corner_detection_worker over the whole image
+ *                 (corner_detection_parallel.cpp:30-105): blurred u8 -> thresholded R
+ *   vo_nms        CornerDetectionParallel::non_maximum_suppression + the manager's sort
+ *                 (corner_detection_parallel.cpp:166-208, feature_extraction_parallel.cpp:276-282)
+ *   vo_describe   FREAK_Parallel::FREAK_feature_description_worker      FREAK_feature_descriptor_parallel.cpp:110
+ */
+int vo_blur(vo_ctx* ctx, const uint8_t* gray, int rows, int cols, uint8_t* blurred);
+int vo_response(vo_ctx* ctx, const uint8_t* blurred, int rows, int cols, float threshold, float* R);
+int vo_nms(vo_ctx* ctx, const float* R, int rows, int cols, int nms_window, int max_keypoints, float* kp_xy,
+           int* n_out);
+int vo_describe(vo_ctx* ctx, const uint8_t* blurred, int rows, int cols, const float* kp_xy, int n,
+                uint8_t* desc512, float* angles);
+
+/* ---- matching ------------------------------------------------------------------------------------
+ * Replaces matchCustomBinaryDescriptorsThreadPool(desc1, desc2, pool, numThreads, ratioThreshold)
+ *   feature_matching_parallel/feature_matching_parallel.cpp:49-113
+ * pairs receives (queryIdx, trainIdx) int32 pairs ascending in queryIdx; cap = capacity in pairs. */
+int vo_match(vo_ctx* ctx, int query_slot, int train_slot, float ratio, int match_bits, int32_t* pairs, int cap,
+             int* n_out);
+/* Host descriptors in the reference's layout (row_bytes 512: one 0/1 byte per test) or packed
+ * (row_bytes 64).  Empty inputs give zero matches, like the reference (:57). */
+int vo_match_host(vo_ctx* ctx, const uint8_t* d1, int n1, const uint8_t* d2, int n2, int row_bytes, float ratio,
+                  int match_bits, int32_t* pairs, int cap, int* n_out);
+/* Per-query (best distance, best index, second-best distance) triples of the last vo_match /
+ * vo_match_host call: n1 x 3 int32; INT32_MAX / -1 where undefined (fewer than 1 / 2 train rows). */
+int vo_match_raw(vo_ctx* ctx, int32_t* raw, int n1);
+
+/* ---- frame sequences (the batched, pipelined form of VisualOdometry::run's front-end half) -------
+ * VisualOdometry.cpp:64-100: extract every frame, match frame i-1 (query) against frame i (train).
+ * Results per frame f: keypoint count, keypoints; per pair f (= frames f, f+1): match count, pairs. */
+typedef struct vo_seq_result {
+    int32_t* n_keypoints; /* [n_frames] */
+    float* kp_xy;         /* [n_frames][max_keypoints][2] or NULL */
+    int32_t* n_matches;   /* [n_frames-1] */
+    int32_t* pairs;       /* [n_frames-1][max_keypoints][2] or NULL */
+} vo_seq_result;
+
+/* Host frames in, host results out; H2D, kernels and D2H are pipelined over `batch`-frame chunks on
+ * separate streams (batch <= n_slots/2). This is the end-to-end path. */
+int vo_sequence_run(vo_ctx* ctx, const uint8_t* frames, int n_frames, int rows, int cols, size_t pitch,
+                    size_t frame_stride, const vo_params* p, int batch, vo_seq_result* out);
+/* Device-resident variant: upload once, then run the kernels only (results stay on the device;
+ * vo_sequence_fetch copies them out).  Used to measure kernel throughput with inputs already in HBM. */
+int vo_sequence_upload(vo_ctx* ctx, const uint8_t* frames, int n_frames, int rows, int cols, size_t pitch,
+                       size_t frame_stride);
+int vo_sequence_run_resident(vo_ctx* ctx, const vo_params* p, int batch);
+int vo_sequence_fetch(vo_ctx* ctx, vo_seq_result* out);
+
+/* ---- measurement hooks ------------------------------------------------------------------------ */
+/* CUDA-event timing on the context's own compute stream. */
+int vo_timer_start(vo_ctx* ctx);
+int vo_timer_stop(vo_ctx* ctx, float* ms); /* synchronises; elapsed since vo_timer_start */
+/* Number of kernel launches issued by this context since creation (or since the last reset). */
+long long vo_launch_count(vo_ctx* ctx, int reset);
+/* Accumulated device time (ms, CUDA events) per kernel family since the last reset, when profiling is
+ * enabled with vo_profile_enable(ctx, 1): [0] stencil, [1] nms, [2] select/sort, [3] freak, [4] match,
+ * [5] match-finalize.  Enabling it inserts events around every launch; leave it off for throughput runs. */
+int vo_profile_enable(vo_ctx* ctx, int on);
+int vo_profile_read(vo_ctx* ctx, float ms[8], long long launches[8], int reset);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VOFRONT_H */

@@ -1,0 +1,75 @@
+import sys
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+ROOT = Path(__file__).resolve().parents[1]
+if str(ROOT) not in sys.path:
+    sys.path.insert(0, str(ROOT))
+GOLDEN = ROOT / "tests" / "golden"
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a B200 (run with -m gpu on the GPU box)")
+
+
+@pytest.fixture(scope="session")
+def oracle():
+    from oracle.pyoracle import Oracle
+    return Oracle()
+
+
+@pytest.fixture(scope="session")
+def reference():
+    """The reference's own code (oracle/_ref/libvoref.so); skipped when it was never built."""
+    from oracle import pyoracle
+    if not pyoracle.reference_available():
+        pytest.skip("oracle/_ref/libvoref.so not available")
+    return pyoracle.Reference()
+
+
+@pytest.fixture(scope="session")
+def factory():
+    import cv2
+    f1 = cv2.imread(str(GOLDEN / "factory1.png"), cv2.IMREAD_GRAYSCALE)
+    f2 = cv2.imread(str(GOLDEN / "factory2.png"), cv2.IMREAD_GRAYSCALE)
+    assert f1 is not None and f1.shape == (480, 752)
+    return f1, f2, dict(np.load(GOLDEN / "factory.npz"))
+
+
+@pytest.fixture(scope="session")
+def kitti_pair():
+    import hashlib
+    from acs_visual_odometry_b200.synth import make_sequence
+    fr = make_sequence(2, seed=7)
+    g = dict(np.load(GOLDEN / "kitti_synth.npz"))
+    same = hashlib.sha256(fr.tobytes()).digest() == g["frames_sha256"].tobytes()
+    return fr, (g if same else None)  # None: numpy's generator stream changed; golden comparison not applicable
+
+
+@pytest.fixture(scope="session")
+def matcher_kat():
+    return dict(np.load(GOLDEN / "matcher_kat.npz"))
+
+
+def unpack(packed):
+    """n x 16 uint32 -> n x 512 bytes (0/1)."""
+    packed = np.ascontiguousarray(packed, np.uint32).reshape(-1, 16)
+    bits = np.unpackbits(packed.view(np.uint8).reshape(-1, 64), axis=1, bitorder="little")
+    return np.ascontiguousarray(bits, np.uint8)
+
+
+def dense_R(idx, val, shape):
+    R = np.zeros(shape, np.float32)
+    R.reshape(-1)[idx] = val
+    return R
+
+
+@pytest.fixture(scope="session")
+def vo_small():
+    """A context for the small GPU parity cases."""
+    from acs_visual_odometry_b200 import VoFront
+    ctx = VoFront(max_rows=480, max_cols=1241, max_keypoints=2048, n_slots=8)
+    yield ctx
+    ctx.close()
