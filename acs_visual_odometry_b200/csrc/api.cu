@@ -276,7 +276,7 @@ void vo_destroy(vo_ctx* c) {
     cudaFree(c->d_kp); cudaFree(c->d_desc); cudaFree(c->d_angles); cudaFree(c->d_nkp); cudaFree(c->d_flags);
     cudaFree(c->d_partial); cudaFree(c->d_raw); cudaFree(c->d_pairs); cudaFree(c->d_nmatch); cudaFree(c->d_bytes);
     cudaFree(c->d_seq); cudaFree(c->d_seq_nkp); cudaFree(c->d_seq_kp); cudaFree(c->d_seq_nmatch); cudaFree(c->d_seq_pairs);
-    cudaFree(c->d_seq_flags);
+    cudaFree(c->d_seq_flags); cudaFree(c->d_stage);
     if (c->h_small) cudaFreeHost(c->h_small);
     delete[] c->slot_rows; delete[] c->slot_cols;
     for (int k = 0; k < 2; ++k) {
@@ -637,17 +637,29 @@ int vo_sequence_run(vo_ctx* c, const uint8_t* frames, int n_frames, int rows, in
     CK(c, cudaSetDevice(c->device));
     if ((rc = ensure_seq_results(c, n_frames))) return rc;
     std::vector<int> flags(n_frames);
-    const bool contiguous = frame_stride == pitch * (size_t)rows && rows == c->max_rows;
+    // Frames that lie back to back in host memory go up with ONE linear copy per chunk into a staging
+    // area that keeps the host layout (the stencil kernel reads any pitch); a strided 2-D copy of
+    // 1241-byte rows runs at a fraction of PCIe bandwidth.
+    const bool contiguous = frame_stride == pitch * (size_t)rows;
+    if (contiguous) {
+        const size_t need = 2 * (size_t)batch * frame_stride;
+        if (need > c->stage_cap) {
+            CK(c, cudaStreamSynchronize(c->s_compute));
+            cudaFree(c->d_stage); c->d_stage = nullptr; c->stage_cap = 0;
+            CK(c, cudaMalloc(&c->d_stage, need));
+            c->stage_cap = need;
+        }
+    }
     int chunk = 0;
     for (int g0 = 0; g0 < n_frames; g0 += batch, ++chunk) {
         const int cnt = n_frames - g0 < batch ? n_frames - g0 : batch;
         const int set = chunk & 1, base = set * batch;
-        uint8_t* dst = c->d_img + (size_t)base * c->img_fstride;
+        uint8_t* dst = contiguous ? c->d_stage + (size_t)set * batch * frame_stride : c->d_img + (size_t)base * c->img_fstride;
+        const size_t dst_fstride = contiguous ? frame_stride : c->img_fstride, dst_pitch = contiguous ? pitch : c->img_pitch;
         // H2D of chunk `chunk` may start once the kernels of chunk-2 (same slot set) have finished
         if (chunk >= 2) CK(c, cudaStreamWaitEvent(c->s_h2d, c->ev_done[set], 0));
         if (contiguous) {
-            CK(c, cudaMemcpy2DAsync(dst, c->img_pitch, frames + (size_t)g0 * frame_stride, pitch, (size_t)cols, (size_t)rows * cnt,
-                                    cudaMemcpyHostToDevice, c->s_h2d));
+            CK(c, cudaMemcpyAsync(dst, frames + (size_t)g0 * frame_stride, (size_t)cnt * frame_stride, cudaMemcpyHostToDevice, c->s_h2d));
         } else {
             for (int k = 0; k < cnt; ++k)
                 CK(c, cudaMemcpy2DAsync(dst + (size_t)k * c->img_fstride, c->img_pitch, frames + (size_t)(g0 + k) * frame_stride, pitch,
@@ -655,7 +667,7 @@ int vo_sequence_run(vo_ctx* c, const uint8_t* frames, int n_frames, int rows, in
         }
         CK(c, cudaEventRecord(c->ev_h2d[set], c->s_h2d));
         CK(c, cudaStreamWaitEvent(c->s_compute, c->ev_h2d[set], 0));
-        if ((rc = run_seq_chunk(c, dst, c->img_fstride, c->img_pitch, g0, cnt, batch, rows, cols, p))) return rc;
+        if ((rc = run_seq_chunk(c, dst, dst_fstride, dst_pitch, g0, cnt, batch, rows, cols, p))) return rc;
         CK(c, cudaEventRecord(c->ev_done[set], c->s_compute));
         // D2H of this chunk's results overlaps the next chunk's kernels
         CK(c, cudaStreamWaitEvent(c->s_d2h, c->ev_done[set], 0));

@@ -48,6 +48,8 @@ struct vo_ctx {
     uint8_t* d_bytes = nullptr;  // scratch: 2 x max_kp x 512 unpacked descriptor bytes / BGR staging
     size_t bytes_cap = 0;
 
+    uint8_t* d_stage = nullptr; size_t stage_cap = 0;  // 2 x batch frames in host layout (vo_sequence_run)
+
     // resident sequence
     uint8_t* d_seq = nullptr; size_t seq_cap = 0;
     int seq_frames = 0, seq_rows = 0, seq_cols = 0; size_t seq_pitch = 0, seq_fstride = 0;

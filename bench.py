@@ -43,43 +43,46 @@ def measured_peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region."""
-    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """SM clock and throttle reasons sampled through NVML every 20 ms while the GPU is under the benchmark load
+    (the timed regions last tens of milliseconds, far below nvidia-smi's useful sampling period)."""
 
     def __init__(self, gpu_index):
-        self.lines, self.proc, self.gpu = [], None, gpu_index
+        self.gpu, self.samples, self._stop, self.thread = gpu_index, [], threading.Event(), None
+
+    def _run(self):
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.gpu)
+            mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            while not self._stop.is_set():
+                sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                self.samples.append((sm, mx, int(r)))
+                time.sleep(0.02)
+            nv.nvmlShutdown()
+        except Exception as e:  # NVML unavailable: report no samples rather than guess
+            self.error = repr(e)
 
     def start(self):
-        try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.gpu}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "200"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            threading.Thread(target=lambda: [self.lines.append(l) for l in self.proc.stdout], daemon=True).start()
-        except Exception:
-            self.proc = None
+        self.thread = threading.Thread(target=self._run, daemon=True)
+        self.thread.start()
 
     def stop(self):
-        if self.proc:
-            self.proc.terminate()
-            try:
-                self.proc.wait(2)
-            except Exception:
-                self.proc.kill()
-        sm, mx, reasons = [], [], set()
-        for l in self.lines:
-            f = [x.strip() for x in l.split(",")]
-            if len(f) < 7:
-                continue
-            try:
-                sm.append(float(f[0])); mx.append(float(f[1]))
-            except ValueError:
-                continue
-            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[3:7]):
-                if v.lower().startswith("active"):
-                    reasons.add(name)
-        if not sm:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
-        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons), "samples": len(sm)}
+        self._stop.set()
+        if self.thread:
+            self.thread.join(2)
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0, "error": getattr(self, "error", None)}
+        bits = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
+        seen = 0
+        for _, _, r in self.samples:
+            seen |= r
+        return {"sm_mhz": float(np.median([x[0] for x in self.samples])), "sm_max_mhz": float(self.samples[0][1]),
+                "reasons": sorted(n for b, n in bits.items() if seen & b), "samples": len(self.samples)}
 
 
 def dist_env():
@@ -200,12 +203,12 @@ def main():
 
     # ---- value: frames resident in HBM, kernels only, CUDA events on the library's launch stream
     vo.sequence_upload(frames)
+    sampler = ClockSampler(local)
+    sampler.start()
     for _ in range(W):
         vo.sequence_run_resident(params, args.batch)
     vo.sync()
-    sampler = ClockSampler(local)
     barrier()
-    sampler.start()
     vo.launch_count(reset=True)
     vo.timer_start()
     for _ in range(args.steps):
@@ -213,7 +216,6 @@ def main():
     ms_total = vo.timer_stop()
     launches = vo.launch_count()
     barrier()
-    clocks = sampler.stop()
     ms_step = max_over_ranks(ms_total / args.steps)
     nk, _, nm, _ = vo.sequence_fetch(want_kp=False, want_pairs=False)
     value = world * n / (ms_step / 1000.0)
@@ -231,6 +233,7 @@ def main():
         vo.sequence_run(frames, params, args.batch, out=out_arrays)   # synchronous: returns when results are on the host
     e2e_ms = max_over_ranks(1000.0 * (time.perf_counter() - t0) / args.steps)
     barrier()
+    clocks = sampler.stop()   # sampled from the first warm-up pass to the end of the end-to-end passes
     e2e_value = world * n / (e2e_ms / 1000.0)
     h2d = n * ROWS * COLS
     d2h = 4 * n + 8 * n * mk + 4 * (n - 1) + 8 * (n - 1) * mk

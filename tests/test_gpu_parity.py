@@ -287,11 +287,11 @@ def test_errors_are_loud(vo_small):
     assert e.value.code == -5
     with pytest.raises(VoError):
         vo_small.describe(img, np.array([[5.0, 5.0]], np.float32))              # outside the FREAK margins
-    # candidate overflow is reported, never truncated: ~1/9 of noise pixels are strict 3x3 maxima
-    noise = np.random.default_rng(1).integers(0, 256, (480, 1241), dtype=np.uint8)
-    vo_small.extract(noise, Params(0.0, 3, 2000), 5)
+    # candidate overflow is reported, never truncated: a lattice of isolated peaks, one per 2x2 cell
+    R = np.zeros((480, 1241), np.float32)
+    R[::2, ::2] = np.arange(240 * 621, dtype=np.float32).reshape(240, 621) + 1.0
     with pytest.raises(VoError) as e:
-        vo_small.fetch(5)
+        vo_small.nms(R, 3, 2000)
     assert e.value.code == -3
     vo_small.extract(img, Params.cpu_ref(), 5)                                  # the context stays usable
     assert len(vo_small.fetch(5)[0]) == 0
