@@ -138,6 +138,17 @@ int ensure_seq_results(vo_ctx* c, int n_frames) {
     return VO_OK;
 }
 
+int ensure_host_flags(vo_ctx* c, int n, int** out) {
+    if (n > c->h_flags_cap) {
+        if (c->h_flags) cudaFreeHost(c->h_flags);
+        c->h_flags = nullptr; c->h_flags_cap = 0;
+        CK(c, cudaMallocHost(&c->h_flags, sizeof(int) * (size_t)n));
+        c->h_flags_cap = n;
+    }
+    *out = c->h_flags;
+    return VO_OK;
+}
+
 // One chunk of a sequence: frames [g0, g0+cnt) already in (or readable through) in_base; extract into the
 // slot set (chunk parity), match pairs (g-1, g), and park the per-frame results in the sequence arrays.
 int run_seq_chunk(vo_ctx* c, const uint8_t* in_base, size_t in_fstride, size_t in_pitch, int g0, int cnt, int batch,
@@ -278,6 +289,7 @@ void vo_destroy(vo_ctx* c) {
     cudaFree(c->d_seq); cudaFree(c->d_seq_nkp); cudaFree(c->d_seq_kp); cudaFree(c->d_seq_nmatch); cudaFree(c->d_seq_pairs);
     cudaFree(c->d_seq_flags); cudaFree(c->d_stage);
     if (c->h_small) cudaFreeHost(c->h_small);
+    if (c->h_flags) cudaFreeHost(c->h_flags);
     delete[] c->slot_rows; delete[] c->slot_cols;
     for (int k = 0; k < 2; ++k) {
         if (c->ev_h2d[k]) cudaEventDestroy(c->ev_h2d[k]);
@@ -636,7 +648,8 @@ int vo_sequence_run(vo_ctx* c, const uint8_t* frames, int n_frames, int rows, in
     if (n_frames > 1 && frame_stride < pitch * (size_t)rows) return fail(c, VO_ERR_BAD_ARG, "frame_stride smaller than a frame");
     CK(c, cudaSetDevice(c->device));
     if ((rc = ensure_seq_results(c, n_frames))) return rc;
-    std::vector<int> flags(n_frames);
+    int* flags = nullptr;
+    if ((rc = ensure_host_flags(c, n_frames, &flags))) return rc;  // pinned: a pageable D2H target would block the host
     // Frames that lie back to back in host memory go up with ONE linear copy per chunk into a staging
     // area that keeps the host layout (the stencil kernel reads any pitch); a strided 2-D copy of
     // 1241-byte rows runs at a fraction of PCIe bandwidth.
@@ -671,7 +684,7 @@ int vo_sequence_run(vo_ctx* c, const uint8_t* frames, int n_frames, int rows, in
         CK(c, cudaEventRecord(c->ev_done[set], c->s_compute));
         // D2H of this chunk's results overlaps the next chunk's kernels
         CK(c, cudaStreamWaitEvent(c->s_d2h, c->ev_done[set], 0));
-        CK(c, cudaMemcpyAsync(flags.data() + g0, c->d_seq_flags + g0, sizeof(int) * cnt, cudaMemcpyDeviceToHost, c->s_d2h));
+        CK(c, cudaMemcpyAsync(flags + g0, c->d_seq_flags + g0, sizeof(int) * cnt, cudaMemcpyDeviceToHost, c->s_d2h));
         if (out->n_keypoints) CK(c, cudaMemcpyAsync(out->n_keypoints + g0, c->d_seq_nkp + g0, sizeof(int) * cnt, cudaMemcpyDeviceToHost, c->s_d2h));
         if (out->kp_xy)
             CK(c, cudaMemcpyAsync(out->kp_xy + (size_t)g0 * c->max_kp * 2, c->d_seq_kp + (size_t)g0 * c->max_kp,
@@ -687,7 +700,7 @@ int vo_sequence_run(vo_ctx* c, const uint8_t* frames, int n_frames, int rows, in
     CK(c, cudaStreamSynchronize(c->s_h2d));
     CK(c, cudaStreamSynchronize(c->s_compute));
     CK(c, cudaStreamSynchronize(c->s_d2h));
-    return check_flags(c, flags.data(), n_frames);
+    return check_flags(c, flags, n_frames);
 }
 
 // ---- measurement ---------------------------------------------------------------------------------------

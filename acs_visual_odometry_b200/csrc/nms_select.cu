@@ -5,8 +5,8 @@
 // largest by the tuple (R, i, j)) and the manager's std::sort by (int y, int x)
 // (feature_extraction_parallel.cpp:276-282).
 //
-//   k_nms     one thread per pixel of the margin box; candidates are appended to a per-frame buffer as
-//             64-bit keys (float bits of R << 32 | i << 16 | j) with a warp-aggregated atomic.
+//   k_nms     16-byte loads, four pixels per lane, zero pixels rejected at once; candidates are appended to a
+//             per-frame buffer as 64-bit keys (float bits of R << 32 | i << 16 | j).
 //             R > 0 on every candidate, so the unsigned order of the keys equals the tuple order.
 //   k_select  one CTA per frame: if more than N candidates, an 8-pass MSB radix select finds the N-th
 //             largest key (keys are unique, so exactly N survive); survivors are reduced to their
@@ -15,29 +15,73 @@
 
 namespace {
 
+constexpr int NMS_ROWS = 4;                       // rows per warp (all loads issued before the first test)
+constexpr int NMS_TILE_PX = 8 * NMS_ROWS * 128;   // pixels per CTA: 8 warps x NMS_ROWS rows x 128 columns
+constexpr int NMS_STAGE = NMS_TILE_PX / 4;        // strict maxima are never 8-adjacent: at most one per 2x2 cell
+
+// One warp scans NMS_ROWS row segments of 128 pixels with 16-byte loads, four pixels per lane.  A zero centre
+// can never be a strict maximum (its neighbours are >= 0), so rows of zeros cost one vector load and one
+// compare per four pixels.  Non-zero centres are tested WITHOUT data-dependent loops: the (2h+1) rows of the
+// window are fetched as three aligned float4 each (L1 hits: the neighbouring lanes load the same lines) and the
+// maximum of the window minus its centre is formed with FMNMX; candidate <=> centre > that maximum, which is
+// exactly "no neighbour >= centre" (corner_detection_parallel.cpp:181-190).
+// Candidates are staged in shared memory and appended to the frame's list with one global atomic per CTA.
+template <int HW>
 __global__ void __launch_bounds__(256) k_nms(const NmsArgs a) {
+    __shared__ unsigned long long s_keys[NMS_STAGE];
+    __shared__ int s_n, s_base;
     const int f = blockIdx.z;
-    const int H = a.rows, W = a.cols, h = a.window / 2;
+    const int H = a.rows, W = a.cols;
+    constexpr int h = HW;
     // i in [h, H-h) and 35 <= i <= H-35 ; j in [h, W-h) and 37 <= j <= W-37
     const int i_lo = max(h, 35), i_hi = min(H - h - 1, H - 35);
     const int j_lo = max(h, 37), j_hi = min(W - h - 1, W - 37);
-    const int i = i_lo + blockIdx.y * blockDim.y + threadIdx.y;
-    const int j = j_lo + blockIdx.x * blockDim.x + threadIdx.x;
-    if (i > i_hi || j > j_hi) return;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int c4 = (j_lo & ~3) + 4 * (blockIdx.x * 32 + lane);  // first of this lane's four columns (16-byte aligned)
+    const int i0 = i_lo + (blockIdx.y * 8 + warp) * NMS_ROWS;
+    if (threadIdx.x == 0) s_n = 0;
+    __syncthreads();
     const float* __restrict__ R = a.R + (size_t)f * a.R_fstride;
-    const float c = R[(size_t)i * a.R_pitch + j];
-    if (!(c > 0.0f)) return;  // thresholded map: a zero centre can never be strictly greater than its neighbours
-    bool is_max = true;
-    for (int n = i - h; n <= i + h && is_max; ++n) {
-        const float* row = R + (size_t)n * a.R_pitch;
-        for (int m = j - h; m <= j + h; ++m)
-            if (!(n == i && m == j) && row[m] >= c) { is_max = false; break; }
+    if (c4 <= j_hi && i0 <= i_hi) {
+        float4 v[NMS_ROWS];
+#pragma unroll
+        for (int k = 0; k < NMS_ROWS; ++k)
+            v[k] = (i0 + k <= i_hi) ? __ldg(reinterpret_cast<const float4*>(R + (size_t)(i0 + k) * a.R_pitch + c4)) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int k = 0; k < NMS_ROWS; ++k) {
+            const float cv[4] = {v[k].x, v[k].y, v[k].z, v[k].w};
+            if (!(cv[0] > 0.f || cv[1] > 0.f || cv[2] > 0.f || cv[3] > 0.f)) continue;
+            const int i = i0 + k;
+            float m[4] = {0.f, 0.f, 0.f, 0.f};  // max over the window without the centre (all values >= 0)
+#pragma unroll
+            for (int dn = -h; dn <= h; ++dn) {
+                const float4* row = reinterpret_cast<const float4*>(R + (size_t)(i + dn) * a.R_pitch + c4);
+                const float4 l = __ldg(row - 1), c = dn == 0 ? v[k] : __ldg(row), r = __ldg(row + 1);
+                const float w[12] = {l.x, l.y, l.z, l.w, c.x, c.y, c.z, c.w, r.x, r.y, r.z, r.w};  // columns c4-4 .. c4+7
+#pragma unroll
+                for (int e = 0; e < 4; ++e)
+#pragma unroll
+                    for (int dm = -h; dm <= h; ++dm)
+                        if (!(dn == 0 && dm == 0)) m[e] = fmaxf(m[e], w[4 + e + dm]);
+            }
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const int j = c4 + e;
+                if (cv[e] > m[e] && j >= j_lo && j <= j_hi) {  // cv > m >= 0 implies cv > 0
+                    const int sp = atomicAdd(&s_n, 1);  // < NMS_STAGE by the 2x2-cell bound
+                    s_keys[sp] = ((unsigned long long)__float_as_uint(cv[e]) << 32) | ((unsigned long long)i << 16) | (unsigned long long)j;
+                }
+            }
+        }
     }
-    if (!is_max) return;
-    const int pos = atomicAdd(&a.cand_count[f], 1);
-    if (pos < a.cand_cap)
-        a.cand[(size_t)f * a.cand_cap + pos] =
-            ((unsigned long long)__float_as_uint(c) << 32) | ((unsigned long long)i << 16) | (unsigned long long)j;
+    __syncthreads();
+    const int cnt = s_n;
+    if (cnt == 0) return;
+    if (threadIdx.x == 0) s_base = atomicAdd(&a.cand_count[f], cnt);
+    __syncthreads();
+    const int base = s_base;
+    for (int q = threadIdx.x; q < cnt; q += 256)
+        if (base + q < a.cand_cap) a.cand[(size_t)f * a.cand_cap + base + q] = s_keys[q];
 }
 
 constexpr int SEL_NT = 1024;
@@ -120,11 +164,19 @@ __global__ void __launch_bounds__(SEL_NT) k_select(const SelectArgs a) {
 
 cudaError_t launch_nms(const NmsArgs& a, int n_frames, cudaStream_t st) {
     const int h = a.window / 2;
-    const int ni = min(a.rows - h - 1, a.rows - 35) - max(h, 35) + 1;
-    const int nj = min(a.cols - h - 1, a.cols - 37) - max(h, 37) + 1;
-    if (ni <= 0 || nj <= 0) return cudaSuccess;  // image smaller than the margins: no candidates
-    const dim3 block(64, 4), grid((nj + 63) / 64, (ni + 3) / 4, n_frames);
-    k_nms<<<grid, block, 0, st>>>(a);
+    const int i_lo = max(h, 35), i_hi = min(a.rows - h - 1, a.rows - 35);
+    const int j_lo = max(h, 37), j_hi = min(a.cols - h - 1, a.cols - 37);
+    if (i_hi < i_lo || j_hi < j_lo) return cudaSuccess;  // image smaller than the margins: no candidates
+    if (a.R_pitch & 3) return cudaErrorInvalidValue;     // rows are read with 16-byte loads
+    const int ncol = j_hi - (j_lo & ~3) + 1, nrow = i_hi - i_lo + 1;
+    const dim3 grid((ncol + 127) / 128, (nrow + 8 * NMS_ROWS - 1) / (8 * NMS_ROWS), n_frames);
+    switch (h) {
+        case 1: k_nms<1><<<grid, 256, 0, st>>>(a); break;
+        case 2: k_nms<2><<<grid, 256, 0, st>>>(a); break;
+        case 3: k_nms<3><<<grid, 256, 0, st>>>(a); break;
+        case 4: k_nms<4><<<grid, 256, 0, st>>>(a); break;
+        default: return cudaErrorInvalidValue;
+    }
     return cudaGetLastError();
 }
 

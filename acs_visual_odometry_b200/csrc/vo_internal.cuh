@@ -60,6 +60,7 @@ struct vo_ctx {
     cudaStream_t s_compute = nullptr, s_h2d = nullptr, s_d2h = nullptr;
     cudaEvent_t ev_h2d[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr}, ev_t0 = nullptr, ev_t1 = nullptr;
     int* h_small = nullptr;  // pinned scratch for counts/flags
+    int* h_flags = nullptr; int h_flags_cap = 0;  // pinned per-frame flags of vo_sequence_run
 
     long long launches = 0;
     bool profiling = false;

@@ -107,7 +107,8 @@ int vo_debug_fetch(vo_ctx* ctx, int slot, int what, void* dst);
  *   vo_blur       cv::GaussianBlur(src, dst, Size(7,7), 0)               feature_extraction_parallel.cpp:223
  *   vo_response   direction_gradients_worker + shitomasi_corner_detection_worker over the whole image
  *                 (corner_detection_parallel.cpp:30-105): blurred u8 -> thresholded R
- *   vo_nms        CornerDetectionParallel::non_maximum_suppression + the manager's sort
+ *   vo_nms        CornerDetectionParallel::non_maximum_suppression + the manager's sort; R must be a thresholded
+ *                 (non-negative) response map, as produced by vo_response
  *                 (corner_detection_parallel.cpp:166-208, feature_extraction_parallel.cpp:276-282)
  *   vo_describe   FREAK_Parallel::FREAK_feature_description_worker      FREAK_feature_descriptor_parallel.cpp:110
  */

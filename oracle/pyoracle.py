@@ -61,6 +61,8 @@ class Oracle:
         lib.vo_oracle_match.argtypes = [_u8p, C.c_int, _u8p, C.c_int, C.c_int, C.c_float, _i32p, _i32p]
         lib.vo_oracle_match.restype = C.c_int
         lib.vo_oracle_pack.argtypes = [_u8p, C.c_int, _u32p]
+        lib.vo_oracle_check_recip_division.argtypes = [C.POINTER(C.c_long)]
+        lib.vo_oracle_check_recip_division.restype = C.c_long
 
     def bgr2gray(self, bgr):
         bgr = np.ascontiguousarray(bgr, np.uint8)
@@ -129,6 +131,11 @@ class Oracle:
         if raw:
             return pairs[:n].copy(), rawbuf[:n1].copy() if n2 > 0 else rawbuf[:0].copy()
         return pairs[:n].copy()
+
+    def check_recip_division(self):
+        total = C.c_long()
+        bad = self.lib.vo_oracle_check_recip_division(C.byref(total))
+        return bad, total.value
 
     def pack(self, desc512):
         d = np.ascontiguousarray(desc512, np.uint8).reshape(-1, 512)

@@ -244,3 +244,27 @@ void vo_oracle_pack(const uint8_t* desc512, int n, uint32_t* packed) {
             packed[(size_t)q * 16 + w] = v;
         }
 }
+
+/* Test helper for the CUDA FREAK kernel's divide-free quotient (acs_visual_odometry_b200/csrc/freak.cu):
+ * q = m*rn; r = fma(-q, n, m); q' = fma(r, rn, q) with rn = RN(1/n).  Compares q' with the IEEE quotient m/n
+ * that compute_orientation (FREAK_feature_descriptor_parallel.cpp:39-40) evaluates, for EVERY pair of
+ * pattern points, every intensity difference -255..255 and both axes.  Returns the number of mismatches. */
+long vo_oracle_check_recip_division(long* total_out) {
+    long bad = 0, total = 0;
+    for (int p = 0; p < VO_FREAK_POINTS; ++p)
+        for (int r = p + 1; r < VO_FREAK_POINTS; ++r) {
+            const float dx = (float)(VO_FREAK_PX[p] - VO_FREAK_PX[r]), dy = (float)(VO_FREAK_PY[p] - VO_FREAK_PY[r]);
+            const float n = sqrtf(dx * dx + dy * dy);
+            const float rn = 1.0f / n;
+            for (int ic = -255; ic <= 255; ++ic)
+                for (int ax = 0; ax < 2; ++ax) {
+                    const float m = (float)ic * (ax ? dy : dx);
+                    const float q = m * rn;
+                    const float got = fmaf(fmaf(-q, n, m), rn, q);
+                    ++total;
+                    if (got != m / n) ++bad;
+                }
+        }
+    if (total_out) *total_out = total;
+    return bad;
+}
