@@ -1,0 +1,87 @@
+// adapter_driver.cpp — TEST PROGRAM: drives include/vofront_adapter.hpp exactly the way the reference's
+// callers drive their front-end (VisualOdometry.cpp:29-36, matching.cpp:116-117,148), and dumps the results
+// for tests/test_cpp_adapter.py to compare with the oracle.  Compiled against oracle/shim's cv:: stand-in
+// (no C++ OpenCV in the image); with real OpenCV the same source compiles unchanged.
+//
+//   adapter_driver <in.raw> <out.bin>
+// in.raw : int32 rows, cols, then two gray u8 images of rows*cols bytes.
+// out.bin: for each of the sections below  int32 count  followed by the payload.
+#include <cstdio>
+#include <cstdlib>
+#include <fstream>
+#include <iostream>
+
+#include <opencv2/core.hpp>
+
+#include "vofront_adapter.hpp"
+
+class thread_pool {};  // the adapter only takes it by reference (the reference's pool: threadpool.h:15)
+
+static void put_i32(std::ofstream& o, int32_t v) { o.write(reinterpret_cast<const char*>(&v), 4); }
+
+static void dump_features(std::ofstream& o, const std::pair<std::vector<std::vector<uint8_t>>, std::vector<cv::KeyPoint>>& f) {
+    put_i32(o, (int32_t)f.second.size());
+    for (const auto& k : f.second) {
+        o.write(reinterpret_cast<const char*>(&k.pt.x), 4);
+        o.write(reinterpret_cast<const char*>(&k.pt.y), 4);
+    }
+    for (const auto& d : f.first) o.write(reinterpret_cast<const char*>(d.data()), 512);
+}
+static void dump_matches(std::ofstream& o, const std::vector<std::pair<int, int>>& m) {
+    put_i32(o, (int32_t)m.size());
+    for (const auto& p : m) { put_i32(o, p.first); put_i32(o, p.second); }
+}
+
+int main(int argc, char** argv) {
+    if (argc != 3) { std::cerr << "usage: adapter_driver in.raw out.bin\n"; return 2; }
+    std::ifstream in(argv[1], std::ios::binary);
+    int32_t rows = 0, cols = 0;
+    in.read(reinterpret_cast<char*>(&rows), 4);
+    in.read(reinterpret_cast<char*>(&cols), 4);
+    cv::Mat img1(rows, cols, CV_8UC1), img2(rows, cols, CV_8UC1);
+    in.read(reinterpret_cast<char*>(img1.data), (std::streamsize)rows * cols);
+    in.read(reinterpret_cast<char*>(img2.data), (std::streamsize)rows * cols);
+    if (!in) { std::cerr << "short input\n"; return 2; }
+    std::ofstream out(argv[2], std::ios::binary);
+    try {
+        // --- 1. the VisualOdometry path: GPU_settings built once, gray frames, ratio 0.75 (VisualOdometry.cpp:9-36)
+        GPU_settings gpu_settings(0, rows, cols, 2000);
+        auto f1 = feature_extraction_manager_with_points(img1, gpu_settings);
+        auto f2 = feature_extraction_manager_with_points(img2, gpu_settings);
+        auto m = matchCustomBinaryDescriptorsThreadPool(f1.first, f2.first, gpu_settings, 0.75f);
+        dump_features(out, f1);
+        dump_features(out, f2);
+        dump_matches(out, m);
+        // --- 2. the thread-pool signatures (matching.cpp:116-117,148): BGR input, pool ignored
+        thread_pool pool1;
+        cv::Mat bgr(rows, cols, CV_8UC3);
+        for (int i = 0; i < rows; ++i)
+            for (int j = 0; j < cols; ++j)
+                for (int c = 0; c < 3; ++c) bgr.data[(size_t)i * bgr.step + 3 * j + c] = img1.data[(size_t)i * img1.step + j];
+        auto g1 = feature_extraction_manager_with_points(bgr, pool1);
+        auto g2 = feature_extraction_manager_with_points(img2, pool1);
+        auto gm = matchCustomBinaryDescriptorsThreadPool(g1.first, g2.first, pool1, 8, 0.75f);
+        dump_features(out, g1);
+        dump_features(out, g2);
+        dump_matches(out, gm);
+        // --- 3. stage entry points
+        cv::Mat blurred = vofront::gaussian_blur7(gpu_settings, img1);
+        auto R = vofront::shitomasi_response(gpu_settings, blurred, 25000.0f);
+        auto kps = vofront::non_maximum_suppression(gpu_settings, R, rows, cols, 5, 1500);
+        auto desc = vofront::FREAK_feature_description(gpu_settings, kps, blurred);
+        dump_features(out, {desc, kps});
+        // --- 4. error behaviour: empty input => empty result (feature_matching_parallel.cpp:57); bad input => std::runtime_error
+        std::vector<std::vector<uint8_t>> none;
+        put_i32(out, (int32_t)matchCustomBinaryDescriptorsThreadPool(none, f2.first, pool1, 8, 0.75f).size());
+        int threw = 0;
+        try {
+            cv::Mat big(rows + 1, cols, CV_8UC1);
+            feature_extraction_manager_with_points(big, gpu_settings);
+        } catch (const std::runtime_error&) { threw = 1; }
+        put_i32(out, threw);
+    } catch (const std::exception& e) {
+        std::cerr << "adapter_driver: " << e.what() << "\n";
+        return 1;
+    }
+    return 0;
+}

@@ -1,0 +1,79 @@
+"""The C++17 adapter (include/vofront_adapter.hpp): the reference's entry points, called from C++ the way
+VisualOdometry.cpp:29-36 and matching.cpp:116-117,148 call them, must give the oracle's results."""
+import struct
+import subprocess
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+ROOT = Path(__file__).resolve().parents[1]
+DRIVER = ROOT / "tests" / "cpp" / "adapter_driver"
+
+
+def build_driver():
+    import __graft_entry__ as g
+    g.build_adapter_driver()
+    return DRIVER
+
+
+def test_adapter_driver_compiles():
+    """CPU box: the adapter header compiles as plain C++17 against cv:: types and links to the C ABI."""
+    assert build_driver().exists()
+
+
+def _read_features(buf, off):
+    (n,) = struct.unpack_from("<i", buf, off)
+    off += 4
+    kp = np.frombuffer(buf, np.float32, 2 * n, off).reshape(n, 2)
+    off += 8 * n
+    d = np.frombuffer(buf, np.uint8, 512 * n, off).reshape(n, 512)
+    return kp, d, off + 512 * n
+
+
+def _read_matches(buf, off):
+    (n,) = struct.unpack_from("<i", buf, off)
+    m = np.frombuffer(buf, np.int32, 2 * n, off + 4).reshape(n, 2)
+    return m, off + 4 + 8 * n
+
+
+@pytest.mark.gpu
+def test_adapter_matches_oracle(tmp_path, oracle, factory):
+    f1, f2, _ = factory
+    build_driver()
+    raw = tmp_path / "in.raw"
+    raw.write_bytes(struct.pack("<ii", *f1.shape) + f1.tobytes() + f2.tobytes())
+    out = tmp_path / "out.bin"
+    r = subprocess.run([str(DRIVER), str(raw), str(out)], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    buf = out.read_bytes()
+    off = 0
+    # 1. GPU_settings signature: VisualOdometry preset (20000 / 3 / 2000), gray input
+    for img in (f1, f2):
+        kp, d, off = _read_features(buf, off)
+        kp_o, d_o = oracle.extract(img, 20000.0, 3, 2000)
+        assert np.array_equal(kp, kp_o)
+        assert (d == d_o).mean() >= 0.9999
+        if img is f1:
+            d1 = d
+        else:
+            d2 = d
+    m, off = _read_matches(buf, off)
+    assert np.array_equal(m, oracle.match(d1, d2, 32, 0.75))
+    # 2. thread_pool signature: CPU preset (25000 / 5 / 1500), BGR input through custom_bgr2gray
+    descs = []
+    for img in (f1, f2):
+        kp, d, off = _read_features(buf, off)
+        kp_o, d_o = oracle.extract(img, 25000.0, 5, 1500)
+        assert np.array_equal(kp, kp_o)
+        assert (d == d_o).mean() >= 0.9999
+        descs.append(d)
+    m, off = _read_matches(buf, off)
+    assert np.array_equal(m, oracle.match(descs[0], descs[1], 32, 0.75))
+    # 3. stage entry points chained by hand = the manager
+    kp, d, off = _read_features(buf, off)
+    kp_o, d_o = oracle.extract(f1, 25000.0, 5, 1500)
+    assert np.array_equal(kp, kp_o) and (d == d_o).mean() >= 0.9999
+    # 4. empty input -> empty result; oversize image -> std::runtime_error
+    n_empty, threw = struct.unpack_from("<ii", buf, off)
+    assert n_empty == 0 and threw == 1
