@@ -659,7 +659,7 @@ int vo_sequence_run(vo_ctx* c, const uint8_t* frames, int n_frames, int rows, in
         if (need > c->stage_cap) {
             CK(c, cudaStreamSynchronize(c->s_compute));
             cudaFree(c->d_stage); c->d_stage = nullptr; c->stage_cap = 0;
-            CK(c, cudaMalloc(&c->d_stage, need));
+            CK(c, cudaMalloc(&c->d_stage, need + 16));  // the stencil reads whole words: up to 7 bytes past a row
             c->stage_cap = need;
         }
     }

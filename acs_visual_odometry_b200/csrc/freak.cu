@@ -9,15 +9,19 @@
 // Mapping: ONE THREAD PER KEYPOINT.  The orientation is a 903-term fp32 sum whose rounding depends on
 // the order, so it is a dependent chain per keypoint; giving every lane its own chain keeps all 32 lanes
 // busy (a warp-per-keypoint layout would idle 30 lanes during the chain).  The 43 unrotated samples sit in
-// shared memory ([point][thread], conflict free); the pair constants (dx, dy, |d|, 1/|d|) are one
-// broadcast 16-byte load per pair; the 43 rotated samples stay in registers and the 512 tests are fully
-// unrolled register compares (freak_tables.h X-macros).
+// shared memory ([point][thread], conflict free).  Per pair the kernel issues six instructions: one shared
+// load, one constant-bank load of the pair's weights through the uniform datapath (no LSU traffic), the
+// intensity difference, and three packed-fp32 operations (FMUL2 / FFMA2 / FADD2) that carry the x and y
+// components together.  Rows of the pair table are padded to multiples of six with zero-weight entries
+// (adding +-0 never changes a sum that started at +0), so the inner loop has no remainder.
 //
 // Exactness: the orientation sums are accumulated in the reference's pair order with one fp32 rounding
-// per operation.  ic*dx is an exact integer; the IEEE quotient (ic*dx)/|d| is obtained without a divide:
-// q = m*rn, r = fma(-q, |d|, m), q' = fma(r, rn, q) with rn = RN(1/|d|) - Markstein's correction, checked
-// EXHAUSTIVELY against m/|d| for all 903 pairs x 511 intensity differences x 2 axes
-// (tests/test_oracle.py::test_reciprocal_division_is_exact).  So O_x and O_y are bit-identical to the CPU.
+// per term.  The reference's term is RN(RN(ic*d) / |d|) with ic*d an exact integer, i.e. RN(ic * w) for the
+// real number w = d/|d|.  Here w is split into wh = RN(w), wl = RN(w - wh) and the term is
+// fma(ic, wh, RN(ic*wl)): the argument of the final rounding is within 2^-47 of ic*w, so the result can
+// differ only if ic*w lies that close to a rounding boundary - checked EXHAUSTIVELY against the IEEE
+// quotient for all 903 pairs x 511 intensity differences x 2 axes: zero mismatches
+// (tests/test_oracle.py::test_split_weight_product_is_exact).  So O_x and O_y are bit-identical to the CPU.
 // The only inexact step is atan2f/cosf/sinf: glibc's are < 1 ulp but not correctly rounded; here they are
 // evaluated in fp64 and rounded once to fp32 (measured: angles differ by at most 1 ulp, descriptor bits
 // identical on every fixture).
@@ -27,10 +31,21 @@
 namespace {
 
 constexpr int FK_NT = 64;
+constexpr int FK_GROUP = 6;  // pairs per inner-loop trip
+// padded pair table: row p holds the pairs (p, r), r = 43 - 6*ceil((42-p)/6) .. 42; entries with r <= p are zero
+constexpr int FK_TABLE = 1008;  // sum over p of 6*ceil((42-p)/6)
 
-__device__ float4 g_pair[VO_FREAK_PAIRS];  // (dx, dy, |d|, RN(1/|d|)) in the reference's lexicographic pair order
+struct __align__(16) PairW { float whx, why, wlx, wly; };
+__constant__ PairW c_w[FK_TABLE];
 __constant__ signed char c_px[VO_FREAK_POINTS];
 __constant__ signed char c_py[VO_FREAK_POINTS];
+
+typedef unsigned long long u64;
+__device__ __forceinline__ u64 pk(float lo, float hi) { u64 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ void upk(u64 v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ u64 fma2(u64 a, u64 b, u64 c) { u64 d; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c)); return d; }
+__device__ __forceinline__ u64 mul2(u64 a, u64 b) { u64 d; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+__device__ __forceinline__ u64 add2(u64 a, u64 b) { u64 d; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
 
 __global__ void __launch_bounds__(FK_NT) k_freak(const FreakArgs a) {
     __shared__ float s_v[VO_FREAK_POINTS][FK_NT];
@@ -49,21 +64,31 @@ __global__ void __launch_bounds__(FK_NT) k_freak(const FreakArgs a) {
 #pragma unroll
     for (int p = 0; p < VO_FREAK_POINTS; ++p) s_v[p][t] = (float)centre[(int)c_py[p] * pitch + (int)c_px[p]];
 
-    float ox = 0.0f, oy = 0.0f;
-    const float4* __restrict__ pc = g_pair;
+    // O += RN(ic * d / |d|) over the 903 pairs in the reference's order; (x, y) components packed.
+    // The product of the packed multiply feeds only the addend of the FMA, and the FMA only the addend of
+    // the sum, so ptxas has nothing to contract.
+    u64 o2 = 0ull;
+    int k = 0;
+#pragma unroll 1
     for (int p = 0; p < VO_FREAK_POINTS - 1; ++p) {
         const float vp = s_v[p][t];
-#pragma unroll 6
-        for (int r = p + 1; r < VO_FREAK_POINTS; ++r) {
-            const float4 c = __ldg(pc++);  // uniform address: one broadcast load
-            const float ic = __fsub_rn(vp, s_v[r][t]);
-            const float mx = __fmul_rn(ic, c.x), my = __fmul_rn(ic, c.y);  // exact integers
-            const float qx = __fmul_rn(mx, c.w), qy = __fmul_rn(my, c.w);
-            const float rx = __fmaf_rn(-qx, c.z, mx), ry = __fmaf_rn(-qy, c.z, my);
-            ox = __fadd_rn(ox, __fmaf_rn(rx, c.w, qx));  // ox += RN((ic*dx)/|d|)
-            oy = __fadd_rn(oy, __fmaf_rn(ry, c.w, qy));
+        const int groups = (VO_FREAK_POINTS - 1 - p + FK_GROUP - 1) / FK_GROUP;
+        const float* sv = &s_v[VO_FREAK_POINTS - FK_GROUP * groups][t];
+#pragma unroll 1
+        for (int g = 0; g < groups; ++g) {
+#pragma unroll
+            for (int i = 0; i < FK_GROUP; ++i) {
+                const PairW w = c_w[k + i];  // uniform index: constant-bank load on the uniform datapath
+                const float ic = __fsub_rn(vp, sv[i * FK_NT]);
+                const u64 ic2 = pk(ic, ic);
+                o2 = add2(o2, fma2(ic2, pk(w.whx, w.why), mul2(ic2, pk(w.wlx, w.wly))));
+            }
+            k += FK_GROUP;
+            sv += FK_GROUP * FK_NT;
         }
     }
+    float ox, oy;
+    upk(o2, ox, oy);
     float angle = 0.0f;
     if (!(isnan(ox) || isnan(oy))) angle = (float)atan2((double)oy, (double)ox);
     a.angles[(size_t)f * a.kp_stride + q] = angle;
@@ -71,21 +96,25 @@ __global__ void __launch_bounds__(FK_NT) k_freak(const FreakArgs a) {
 
     // rotated samples: rm = {cos, -sin, sin, cos}; x' = (int)(kx + px*rm0 + py*rm2); y' = (int)(ky + (-1)*px*rm1 + py*rm3)
     // (-1)*px*rm1 = (-px)*(-sin) = RN(px*sin) exactly, so the products below are the reference's.
-    float v[VO_FREAK_POINTS];
+    int v[VO_FREAK_POINTS];
 #define VO_SAMPLE(i, PX, PY)                                                                             \
     {                                                                                                    \
         const float fx = __fadd_rn(__fadd_rn(kp.x, __fmul_rn((float)(PX), cs)), __fmul_rn((float)(PY), sn)); \
         const float fy = __fadd_rn(__fadd_rn(kp.y, __fmul_rn((float)(PX), sn)), __fmul_rn((float)(PY), cs)); \
-        v[i] = (float)img[(size_t)(int)fy * a.blur_pitch + (int)fx]; /* truncation toward zero */           \
+        v[i] = img[(int)fy * pitch + (int)fx]; /* truncation toward zero */                               \
     }
     VO_FREAK_POINT_LIST(VO_SAMPLE)
 #undef VO_SAMPLE
+    // test j: bit = v[A] > v[B] = sign of v[B] - v[A]; one subtract and one funnel shift push it into the word
+    // (first test ends up in bit 31: the word is bit-reversed once at the end)
     uint32_t w[16];
 #pragma unroll
-    for (int k = 0; k < 16; ++k) w[k] = 0u;
-#define VO_TEST(j, A, B) w[(j) >> 5] |= (v[A] > v[B] ? 1u : 0u) << ((j) & 31);
+    for (int i = 0; i < 16; ++i) w[i] = 0u;
+#define VO_TEST(j, A, B) w[(j) >> 5] = __funnelshift_l(static_cast<uint32_t>(v[B] - v[A]), w[(j) >> 5], 1);
     VO_FREAK_TEST_LIST(VO_TEST)
 #undef VO_TEST
+#pragma unroll
+    for (int i = 0; i < 16; ++i) w[i] = __brev(w[i]);
     uint4* __restrict__ out = reinterpret_cast<uint4*>(a.desc + ((size_t)f * a.kp_stride + q) * 16);
     out[0] = make_uint4(w[0], w[1], w[2], w[3]);
     out[1] = make_uint4(w[4], w[5], w[6], w[7]);
@@ -118,16 +147,26 @@ __global__ void k_unpack(const uint32_t* __restrict__ packed, int n, uint8_t* __
 }  // namespace
 
 cudaError_t freak_upload_tables() {
-    static float4 pairs[VO_FREAK_PAIRS];
+    static PairW tab[FK_TABLE];
     int k = 0;
-    for (int p = 0; p < VO_FREAK_POINTS; ++p)
-        for (int r = p + 1; r < VO_FREAK_POINTS; ++r, ++k) {
-            const float fx = (float)(VO_FREAK_PX[p] - VO_FREAK_PX[r]), fy = (float)(VO_FREAK_PY[p] - VO_FREAK_PY[r]);
-            const float nm = sqrtf(fx * fx + fy * fy);  // IEEE sqrt on exact small integers, as the reference computes it
-            pairs[k] = make_float4(fx, fy, nm, 1.0f / nm);  // IEEE reciprocal (host arithmetic, no fast-math)
+    for (int p = 0; p < VO_FREAK_POINTS - 1; ++p) {
+        const int groups = (VO_FREAK_POINTS - 1 - p + FK_GROUP - 1) / FK_GROUP;
+        for (int r = VO_FREAK_POINTS - FK_GROUP * groups; r < VO_FREAK_POINTS; ++r, ++k) {
+            PairW w = {0.f, 0.f, 0.f, 0.f};
+            if (r > p) {
+                const float fx = (float)(VO_FREAK_PX[p] - VO_FREAK_PX[r]), fy = (float)(VO_FREAK_PY[p] - VO_FREAK_PY[r]);
+                const float nm = sqrtf(fx * fx + fy * fy);  // IEEE sqrt on exact small integers, as the reference computes it
+                // w = d / |d| split into RN(w) and RN(w - RN(w)); host IEEE double arithmetic, no fast-math
+                const double wx = (double)fx / (double)nm, wy = (double)fy / (double)nm;
+                w.whx = (float)wx; w.wlx = (float)(wx - (double)w.whx);
+                w.why = (float)wy; w.wly = (float)(wy - (double)w.why);
+            }
+            tab[k] = w;
         }
+    }
+    if (k != FK_TABLE) return cudaErrorInvalidValue;
     cudaError_t e;
-    if ((e = cudaMemcpyToSymbol(g_pair, pairs, sizeof(pairs))) != cudaSuccess) return e;
+    if ((e = cudaMemcpyToSymbol(c_w, tab, sizeof(tab))) != cudaSuccess) return e;
     if ((e = cudaMemcpyToSymbol(c_px, VO_FREAK_PX, sizeof(VO_FREAK_PX))) != cudaSuccess) return e;
     if ((e = cudaMemcpyToSymbol(c_py, VO_FREAK_PY, sizeof(VO_FREAK_PY))) != cudaSuccess) return e;
     return cudaSuccess;

@@ -63,6 +63,8 @@ class Oracle:
         lib.vo_oracle_pack.argtypes = [_u8p, C.c_int, _u32p]
         lib.vo_oracle_check_recip_division.argtypes = [C.POINTER(C.c_long)]
         lib.vo_oracle_check_recip_division.restype = C.c_long
+        lib.vo_oracle_check_split_weight.argtypes = [C.POINTER(C.c_long)]
+        lib.vo_oracle_check_split_weight.restype = C.c_long
 
     def bgr2gray(self, bgr):
         bgr = np.ascontiguousarray(bgr, np.uint8)
@@ -135,6 +137,11 @@ class Oracle:
     def check_recip_division(self):
         total = C.c_long()
         bad = self.lib.vo_oracle_check_recip_division(C.byref(total))
+        return bad, total.value
+
+    def check_split_weight(self):
+        total = C.c_long()
+        bad = self.lib.vo_oracle_check_split_weight(C.byref(total))
         return bad, total.value
 
     def pack(self, desc512):

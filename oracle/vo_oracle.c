@@ -268,3 +268,33 @@ long vo_oracle_check_recip_division(long* total_out) {
     if (total_out) *total_out = total;
     return bad;
 }
+
+/* ---- exhaustive proof of the FREAK kernel's split-weight product ------------------------------------------
+ * TEST INFRASTRUCTURE.  csrc/freak.cu evaluates the orientation term RN(RN(ic*d)/n) (n = sqrtf(dx^2+dy^2),
+ * FREAK_feature_descriptor_parallel.cpp:39-40) as fma(ic, wh, RN(ic*wl)) with w = (double)d/(double)n,
+ * wh = (float)w, wl = (float)(w - wh).  Compares the two for EVERY pair of pattern points, every intensity
+ * difference -255..255 and both axes.  Returns the number of mismatches. */
+long vo_oracle_check_split_weight(long* total_out) {
+    long bad = 0, total = 0;
+    for (int p = 0; p < VO_FREAK_POINTS; ++p)
+        for (int r = p + 1; r < VO_FREAK_POINTS; ++r) {
+            const float dx = (float)(VO_FREAK_PX[p] - VO_FREAK_PX[r]), dy = (float)(VO_FREAK_PY[p] - VO_FREAK_PY[r]);
+            const float n = sqrtf(dx * dx + dy * dy);
+            for (int ax = 0; ax < 2; ++ax) {
+                const float d = ax ? dy : dx;
+                const double w = (double)d / (double)n;
+                const float wh = (float)w;
+                const float wl = (float)(w - (double)wh);
+                for (int ic = -255; ic <= 255; ++ic) {
+                    const float fic = (float)ic;
+                    const float m = fic * d;
+                    const float tl = fic * wl;
+                    const float got = fmaf(fic, wh, tl);
+                    ++total;
+                    if (got != m / n) ++bad;
+                }
+            }
+        }
+    if (total_out) *total_out = total;
+    return bad;
+}

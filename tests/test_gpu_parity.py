@@ -59,6 +59,36 @@ def test_response_bit_exact(vo_small, oracle, factory, kitti_pair):
     assert bits_equal(R, dense_R(g["factory1_R_idx"], g["factory1_R_val"], R.shape))
 
 
+def test_stencil_border_shapes(vo_small, oracle):
+    """Widths around the 112-column strip and the 4-pixel lane groups, heights around the 4-row trips:
+    every way the mirrored border can fall inside a warp."""
+    rng = np.random.default_rng(5)
+    shapes = [(8, 16), (9, 17), (13, 19), (16, 23), (21, 104), (12, 105), (11, 111), (10, 112), (9, 113), (23, 118),
+              (8, 119), (14, 120), (17, 121), (15, 127), (31, 224), (33, 225), (37, 231), (29, 233), (61, 449)]
+    for shape in shapes:
+        img = rng.integers(0, 256, shape, dtype=np.uint8)
+        b_o = oracle.blur(img)
+        got = vo_small.blur(img)
+        assert np.array_equal(got, b_o), report_mismatch(f"blur {shape}", got, b_o)
+        got, want = vo_small.response(b_o, 0.0), oracle.response(b_o, 0.0)
+        assert bits_equal(got, want), report_mismatch(f"response {shape}", got, want)
+
+
+def test_sequence_unaligned_rows(oracle):
+    """Frames whose host pitch is not a multiple of 4 are read in place (two-word loads + funnel shift)."""
+    from acs_visual_odometry_b200 import Params, VoFront
+    from acs_visual_odometry_b200.synth import make_sequence
+    for rows, cols in ((131, 323), (96, 241)):
+        frames = make_sequence(5, rows, cols, seed=9, n_rects=200)
+        p = Params(20000.0, 3, 300)
+        with VoFront(rows, cols, 300, 8) as vo:
+            nk, kp, nm, pr = vo.sequence_run(frames, p, 2)
+            for k in range(5):
+                kp_o, _ = oracle.extract(frames[k], p.threshold, 3, 300)
+                assert nk[k] == len(kp_o) and np.array_equal(kp[k, :nk[k]], kp_o), (rows, cols, k)
+            assert nk.min() > 10
+
+
 def test_response_handles_saturated_gradients(vo_small, oracle):
     """Checkerboards / step edges drive Jx, Jy to their extremes (|J| up to 1020, sums near 2^23)."""
     yy, xx = np.mgrid[0:96, 0:128]
