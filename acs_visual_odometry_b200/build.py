@@ -54,5 +54,36 @@ def build(force=False, verbose=False):
     return LIB
 
 
+HOST = PKG / "host"
+HOST_LIB = PKG / "libvohost.so"
+HOST_MAIN = PKG / "vo_main"
+HOST_SOURCES = ["vo_ransac.cpp", "vo_pose.cpp", "vo_image_io.cpp", "vo_pipeline.cpp", "vo_host_abi.cpp"]
+CXX = os.environ.get("CXX", "g++")
+CXXFLAGS = ["-std=c++17", "-O2", "-fPIC", "-ffp-contract=off", "-Wall", "-pthread"]
+
+
+def build_host(force=False):
+    """libvohost.so (RANSAC, pose, formats, pipelined VisualOdometry driver; C ABI of include/vohost.h) and the
+    vo_main command line, both linked against libvofront.so."""
+    build(force=False)
+    srcs = [HOST / s for s in HOST_SOURCES]
+    deps = srcs + list(HOST.glob("*.hpp")) + [PKG.parent / "include" / "vohost.h", PKG.parent / "include" / "vofront.h", LIB]
+    newest = max(d.stat().st_mtime for d in deps)
+    rpath = "-Wl,-rpath,$ORIGIN"
+    if force or not HOST_LIB.exists() or HOST_LIB.stat().st_mtime < newest:
+        cmd = [CXX, *CXXFLAGS, "-shared", "-o", str(HOST_LIB), *map(str, srcs), f"-L{PKG}", "-lvofront", "-lz", rpath]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode:
+            raise RuntimeError(f"host library build failed:\n{r.stdout}\n{r.stderr}")
+    main_src = HOST / "vo_main.cpp"
+    if force or not HOST_MAIN.exists() or HOST_MAIN.stat().st_mtime < max(newest, main_src.stat().st_mtime, HOST_LIB.stat().st_mtime):
+        cmd = [CXX, *CXXFLAGS, "-o", str(HOST_MAIN), str(main_src), f"-L{PKG}", "-lvohost", "-lvofront", rpath]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode:
+            raise RuntimeError(f"vo_main build failed:\n{r.stdout}\n{r.stderr}")
+    return HOST_LIB
+
+
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv, verbose=True))
+    print(build_host(force="--force" in sys.argv))

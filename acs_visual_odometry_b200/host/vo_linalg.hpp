@@ -1,0 +1,172 @@
+// vo_linalg.hpp — the small dense double-precision linear algebra the host side of the pipeline needs
+// (the reference uses Eigen in ransac.cpp and OpenCV core/calib3d in PoseUpdate.hpp; neither exists in
+// this image, and the host rows of SURVEY.md section 8f ask for an Eigen/OpenCV-free build).
+// Header-only, no dependencies beyond <cmath>.
+#pragma once
+#include <algorithm>
+#include <array>
+#include <cmath>
+#include <vector>
+
+namespace vo {
+
+struct Vec3 {
+    double v[3];
+    double& operator()(int i) { return v[i]; }
+    double operator()(int i) const { return v[i]; }
+};
+
+struct Mat3 {
+    double m[9];  // row-major
+    double& operator()(int r, int c) { return m[3 * r + c]; }
+    double operator()(int r, int c) const { return m[3 * r + c]; }
+    static Mat3 zero() { Mat3 a; for (double& x : a.m) x = 0.0; return a; }
+    static Mat3 identity() { Mat3 a = zero(); a(0, 0) = a(1, 1) = a(2, 2) = 1.0; return a; }
+};
+
+struct Mat4 {
+    double m[16];  // row-major
+    double& operator()(int r, int c) { return m[4 * r + c]; }
+    double operator()(int r, int c) const { return m[4 * r + c]; }
+    static Mat4 identity() { Mat4 a; for (double& x : a.m) x = 0.0; a(0, 0) = a(1, 1) = a(2, 2) = a(3, 3) = 1.0; return a; }
+};
+
+inline Mat3 mul(const Mat3& a, const Mat3& b) {
+    Mat3 c = Mat3::zero();
+    for (int i = 0; i < 3; ++i)
+        for (int k = 0; k < 3; ++k)
+            for (int j = 0; j < 3; ++j) c(i, j) += a(i, k) * b(k, j);
+    return c;
+}
+inline Vec3 mul(const Mat3& a, const Vec3& x) {
+    Vec3 y;
+    for (int i = 0; i < 3; ++i) y(i) = a(i, 0) * x(0) + a(i, 1) * x(1) + a(i, 2) * x(2);
+    return y;
+}
+inline Mat3 transpose(const Mat3& a) {
+    Mat3 t;
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) t(i, j) = a(j, i);
+    return t;
+}
+inline Mat3 scaled(const Mat3& a, double s) { Mat3 b = a; for (double& x : b.m) x *= s; return b; }
+inline double det(const Mat3& a) {
+    return a(0, 0) * (a(1, 1) * a(2, 2) - a(1, 2) * a(2, 1)) - a(0, 1) * (a(1, 0) * a(2, 2) - a(1, 2) * a(2, 0)) +
+           a(0, 2) * (a(1, 0) * a(2, 1) - a(1, 1) * a(2, 0));
+}
+inline double frobenius(const Mat3& a) { double s = 0; for (double x : a.m) s += x * x; return std::sqrt(s); }
+inline double dot(const Vec3& a, const Vec3& b) { return a(0) * b(0) + a(1) * b(1) + a(2) * b(2); }
+inline double norm(const Vec3& a) { return std::sqrt(dot(a, a)); }
+inline Vec3 cross(const Vec3& a, const Vec3& b) {
+    return Vec3{{a(1) * b(2) - a(2) * b(1), a(2) * b(0) - a(0) * b(2), a(0) * b(1) - a(1) * b(0)}};
+}
+
+inline Mat4 mul(const Mat4& a, const Mat4& b) {
+    Mat4 c; for (double& x : c.m) x = 0.0;
+    for (int i = 0; i < 4; ++i)
+        for (int k = 0; k < 4; ++k)
+            for (int j = 0; j < 4; ++j) c(i, j) += a(i, k) * b(k, j);
+    return c;
+}
+// inverse of a rigid/affine 4x4 whose last row is (0,0,0,1): general 3x3 inverse of the upper block
+inline Mat4 inverse_affine(const Mat4& a) {
+    Mat3 r;
+    for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) r(i, j) = a(i, j);
+    const double d = det(r);
+    Mat3 inv;
+    inv(0, 0) = (r(1, 1) * r(2, 2) - r(1, 2) * r(2, 1)) / d; inv(0, 1) = (r(0, 2) * r(2, 1) - r(0, 1) * r(2, 2)) / d;
+    inv(0, 2) = (r(0, 1) * r(1, 2) - r(0, 2) * r(1, 1)) / d; inv(1, 0) = (r(1, 2) * r(2, 0) - r(1, 0) * r(2, 2)) / d;
+    inv(1, 1) = (r(0, 0) * r(2, 2) - r(0, 2) * r(2, 0)) / d; inv(1, 2) = (r(0, 2) * r(1, 0) - r(0, 0) * r(1, 2)) / d;
+    inv(2, 0) = (r(1, 0) * r(2, 1) - r(1, 1) * r(2, 0)) / d; inv(2, 1) = (r(0, 1) * r(2, 0) - r(0, 0) * r(2, 1)) / d;
+    inv(2, 2) = (r(0, 0) * r(1, 1) - r(0, 1) * r(1, 0)) / d;
+    Mat4 out = Mat4::identity();
+    for (int i = 0; i < 3; ++i) {
+        for (int j = 0; j < 3; ++j) out(i, j) = inv(i, j);
+        out(i, 3) = -(inv(i, 0) * a(0, 3) + inv(i, 1) * a(1, 3) + inv(i, 2) * a(2, 3));
+    }
+    return out;
+}
+
+// One-sided (Hestenes) Jacobi SVD of a row-major m x n matrix, any m >= 1, n <= 16.
+//   A = U diag(s) V^T, singular values sorted in descending order.
+// Outputs: s[n], V (n x n, row-major, columns = right singular vectors), and, if `Uout` is given, the
+// n columns A v_i / s_i (m x n, row-major; columns with s_i == 0 are left as zero).
+// The null vector the 8-point algorithm needs is column n-1 of V (also when m < n: the working columns
+// live in R^m, so at least n - m of them converge to zero).
+inline void jacobi_svd(const double* A, int m, int n, double* s, double* V, double* Uout = nullptr) {
+    std::vector<double> W(A, A + (size_t)m * n);  // working copy; columns converge to u_i * s_i
+    for (int i = 0; i < n; ++i) for (int j = 0; j < n; ++j) V[i * n + j] = i == j ? 1.0 : 0.0;
+    const double eps = 1e-15;
+    for (int sweep = 0; sweep < 60; ++sweep) {
+        bool rotated = false;
+        for (int p = 0; p < n - 1; ++p)
+            for (int q = p + 1; q < n; ++q) {
+                double alpha = 0, beta = 0, gamma = 0;
+                for (int i = 0; i < m; ++i) {
+                    const double wp = W[(size_t)i * n + p], wq = W[(size_t)i * n + q];
+                    alpha += wp * wp; beta += wq * wq; gamma += wp * wq;
+                }
+                if (gamma == 0.0 || std::fabs(gamma) <= eps * std::sqrt(alpha * beta)) continue;
+                rotated = true;
+                const double zeta = (beta - alpha) / (2.0 * gamma);
+                const double t = (zeta >= 0 ? 1.0 : -1.0) / (std::fabs(zeta) + std::sqrt(1.0 + zeta * zeta));
+                const double c = 1.0 / std::sqrt(1.0 + t * t), sn = c * t;
+                for (int i = 0; i < m; ++i) {
+                    const double wp = W[(size_t)i * n + p], wq = W[(size_t)i * n + q];
+                    W[(size_t)i * n + p] = c * wp - sn * wq;
+                    W[(size_t)i * n + q] = sn * wp + c * wq;
+                }
+                for (int i = 0; i < n; ++i) {
+                    const double vp = V[i * n + p], vq = V[i * n + q];
+                    V[i * n + p] = c * vp - sn * vq;
+                    V[i * n + q] = sn * vp + c * vq;
+                }
+            }
+        if (!rotated) break;
+    }
+    std::array<double, 16> nrm{};
+    std::array<int, 16> order{};
+    for (int j = 0; j < n; ++j) {
+        double a = 0;
+        for (int i = 0; i < m; ++i) a += W[(size_t)i * n + j] * W[(size_t)i * n + j];
+        nrm[j] = std::sqrt(a); order[j] = j;
+    }
+    std::stable_sort(order.begin(), order.begin() + n, [&](int a, int b) { return nrm[a] > nrm[b]; });
+    std::vector<double> Vs((size_t)n * n);
+    for (int j = 0; j < n; ++j) {
+        s[j] = nrm[order[j]];
+        for (int i = 0; i < n; ++i) Vs[(size_t)i * n + j] = V[i * n + order[j]];
+    }
+    std::copy(Vs.begin(), Vs.end(), V);
+    if (Uout)
+        for (int j = 0; j < n; ++j)
+            for (int i = 0; i < m; ++i) Uout[(size_t)i * n + j] = s[j] > 0 ? W[(size_t)i * n + order[j]] / s[j] : 0.0;
+}
+
+// Full SVD of a 3x3 matrix: A = U diag(s) V^T with orthogonal U and V (columns of U for vanishing singular
+// values are completed to an orthonormal basis), s descending.
+inline void svd3(const Mat3& A, Mat3& U, Vec3& s, Mat3& V) {
+    double u[9], vv[9], sv[3];
+    jacobi_svd(A.m, 3, 3, sv, vv, u);
+    for (int i = 0; i < 9; ++i) { U.m[i] = u[i]; V.m[i] = vv[i]; }
+    for (int i = 0; i < 3; ++i) s(i) = sv[i];
+    const double tiny = 1e-14 * (sv[0] > 0 ? sv[0] : 1.0);
+    auto col = [&](const Mat3& M, int j) { return Vec3{{M(0, j), M(1, j), M(2, j)}}; };
+    auto setcol = [&](Mat3& M, int j, const Vec3& x) { M(0, j) = x(0); M(1, j) = x(1); M(2, j) = x(2); };
+    if (sv[0] <= tiny) { U = Mat3::identity(); return; }
+    if (sv[1] <= tiny) {  // rank 1: any unit vector orthogonal to u0
+        const Vec3 u0 = col(U, 0);
+        Vec3 a = std::fabs(u0(0)) < 0.9 ? Vec3{{1, 0, 0}} : Vec3{{0, 1, 0}};
+        Vec3 u1 = cross(u0, a);
+        const double n1 = norm(u1);
+        for (int i = 0; i < 3; ++i) u1(i) /= n1;
+        setcol(U, 1, u1);
+        setcol(U, 2, cross(u0, u1));
+        return;
+    }
+    if (sv[2] <= tiny) {  // rank 2: u2 = +-(u0 x u1), sign chosen so that det(U) det(V) > 0 is not forced
+        setcol(U, 2, cross(col(U, 0), col(U, 1)));
+    }
+}
+
+}  // namespace vo

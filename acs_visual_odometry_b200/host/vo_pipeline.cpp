@@ -1,0 +1,357 @@
+// vo_pipeline.cpp — see vo_pipeline.hpp.  Calls the GPU front end only through the C ABI (include/vofront.h).
+#include "vo_pipeline.hpp"
+
+#include <atomic>
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <future>
+#include <stdexcept>
+#include <thread>
+
+namespace vo {
+namespace {
+
+double now_s() {
+    return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+// fn(i) for i in [0, n) on up to `threads` host threads (dynamic distribution)
+template <class Fn>
+void parallel_for(size_t n, size_t threads, Fn fn) {
+    if (threads < 1) threads = 1;
+    if (threads > n) threads = n;
+    if (threads <= 1) { for (size_t i = 0; i < n; ++i) fn(i); return; }
+    std::atomic<size_t> next{0};
+    std::vector<std::thread> pool;
+    pool.reserve(threads);
+    for (size_t t = 0; t < threads; ++t)
+        pool.emplace_back([&] { for (size_t i = next++; i < n; i = next++) fn(i); });
+    for (auto& th : pool) th.join();
+}
+
+void check(vo_ctx* ctx, int rc, const char* what) {
+    if (rc == VO_OK) return;
+    throw std::runtime_error(std::string(what) + ": " + vo_last_error(ctx));
+}
+
+}  // namespace
+
+struct VisualOdometry::PairResult {
+    enum Status { OK, FEW_MATCHES, FEW_INLIERS, DEGENERATE } status = FEW_MATCHES;
+    Mat3 R = Mat3::identity();
+    Vec3 t{{0, 0, 0}};  // unit length; scaled with the ground-truth step in the composition stage
+    int n_matches = 0, n_inliers = 0, iterations = 0;
+};
+
+VisualOdometry::VisualOdometry(const std::string&, std::size_t num_threads, int device)
+    : number_of_threads_(num_threads ? num_threads : 1), device_(device) {
+    vo_params_preset(&params, VO_PRESET_VO_GPU_REF);
+}
+
+VisualOdometry::~VisualOdometry() {
+    if (ctx_) vo_destroy(ctx_);
+}
+
+void VisualOdometry::ensure_ctx(int rows, int cols) {
+    if (ctx_ && rows <= ctx_rows_ && cols <= ctx_cols_) return;
+    if (ctx_) { vo_destroy(ctx_); ctx_ = nullptr; }
+    const int slots = 2 * (batch + 1) + 2;  // two chunk sets of batch+1 frames, plus two for on-demand pairs
+    const int rc = vo_create(&ctx_, device_, rows, cols, params.max_keypoints, slots);
+    if (rc != VO_OK) {
+        const std::string msg = vo_last_error(nullptr);
+        ctx_ = nullptr;
+        throw std::runtime_error("vo_create failed: " + msg);  // like the reference's "No OpenCL devices found" (VisualOdometry.cpp:18)
+    }
+    ctx_rows_ = rows; ctx_cols_ = cols;
+}
+
+// VisualOdometry.cpp:28-31
+std::pair<std::vector<std::vector<uint8_t>>, std::vector<KeyPoint>> VisualOdometry::compute_descriptor_with_key_points(const GrayImage& image) {
+    std::pair<std::vector<std::vector<uint8_t>>, std::vector<KeyPoint>> out;
+    if (image.empty()) return out;
+    ensure_ctx(image.rows, image.cols);
+    check(ctx_, vo_extract(ctx_, image.data.data(), image.rows, image.cols, static_cast<size_t>(image.cols), &params, 0), "vo_extract");
+    int n = 0;
+    std::vector<float> kp(2 * static_cast<size_t>(params.max_keypoints));
+    std::vector<uint8_t> desc(512 * static_cast<size_t>(params.max_keypoints));
+    check(ctx_, vo_frame_fetch(ctx_, 0, &n, kp.data(), desc.data(), nullptr), "vo_frame_fetch");
+    out.first.resize(n);
+    out.second.resize(n);
+    for (int i = 0; i < n; ++i) {
+        out.first[i].assign(desc.begin() + 512 * static_cast<size_t>(i), desc.begin() + 512 * static_cast<size_t>(i + 1));
+        out.second[i].pt.x = kp[2 * i]; out.second[i].pt.y = kp[2 * i + 1];
+    }
+    return out;
+}
+
+// VisualOdometry.cpp:34-36
+std::vector<std::pair<int, int>> VisualOdometry::match_descriptors(const std::vector<std::vector<uint8_t>>& d1,
+                                                                   const std::vector<std::vector<uint8_t>>& d2) {
+    std::vector<std::pair<int, int>> out;
+    if (d1.empty() || d2.empty()) return out;
+    if (!ctx_) throw std::runtime_error("match_descriptors before any extraction: no context");
+    auto flatten = [](const std::vector<std::vector<uint8_t>>& d) {
+        std::vector<uint8_t> f(d.size() * 512);
+        for (size_t i = 0; i < d.size(); ++i) {
+            if (d[i].size() != 512) throw std::runtime_error("descriptor rows must hold 512 bytes");
+            std::memcpy(&f[i * 512], d[i].data(), 512);
+        }
+        return f;
+    };
+    const std::vector<uint8_t> f1 = flatten(d1), f2 = flatten(d2);
+    std::vector<int32_t> pairs(2 * d1.size());
+    int n = 0;
+    check(ctx_, vo_match_host(ctx_, f1.data(), static_cast<int>(d1.size()), f2.data(), static_cast<int>(d2.size()), 512,
+                              params.ratio, params.match_bits, pairs.data(), static_cast<int>(d1.size()), &n), "vo_match_host");
+    out.resize(n);
+    for (int i = 0; i < n; ++i) out[i] = {pairs[2 * i], pairs[2 * i + 1]};
+    return out;
+}
+
+// VisualOdometry.cpp:108-177 for one frame pair: matched points -> RANSAC -> inliers -> getPose (unit translation)
+void VisualOdometry::solve_pair(const float* kp1, const float* kp2, const int32_t* pairs, int n_matches, size_t pair_index,
+                                PairResult& out) const {
+    out = PairResult();
+    out.n_matches = n_matches;
+    if (n_matches < 8) { out.status = PairResult::FEW_MATCHES; return; }
+    std::vector<PointPair> matched(static_cast<size_t>(n_matches));
+    for (int m = 0; m < n_matches; ++m) {
+        const int i1 = pairs[2 * m], i2 = pairs[2 * m + 1];
+        matched[m] = {Point{static_cast<double>(kp1[2 * i1]), static_cast<double>(kp1[2 * i1 + 1])},
+                      Point{static_cast<double>(kp2[2 * i2]), static_cast<double>(kp2[2 * i2 + 1])}};
+    }
+    FundamentalMatrix model;  // fresh per pair (the reference reuses one object across frames, VisualOdometry.cpp:49)
+    Ransac ransac;
+    const RansacStats rs = ransac.run(model, matched, ransac_probability, sampson_threshold, static_cast<int>(number_of_threads_),
+                                      seed ? seed + pair_index : 0);
+    out.iterations = rs.iterations;
+    const auto& inl = model.getInliers();
+    out.n_inliers = static_cast<int>(inl.size());
+    if (inl.size() < 8) { out.status = PairResult::FEW_INLIERS; return; }
+    std::vector<Point2f> p1(inl.size()), p2(inl.size());
+    for (size_t i = 0; i < inl.size(); ++i) {
+        p1[i] = Point2f{static_cast<float>(inl[i].first.x), static_cast<float>(inl[i].first.y)};
+        p2[i] = Point2f{static_cast<float>(inl[i].second.x), static_cast<float>(inl[i].second.y)};
+    }
+    try {
+        PoseUpdate estimator;
+        const PoseResult pr = estimator.getPoseEx(model.getMatrix(), p1, p2, 1.0);
+        out.R = pr.R; out.t = pr.t;
+        out.status = PairResult::OK;
+    } catch (const std::runtime_error&) {
+        out.status = PairResult::DEGENERATE;  // the reference would terminate on the uncaught exception
+    }
+}
+
+namespace {
+
+struct Chunk {
+    size_t first = 0, last = 0;   // frame indices [first, last) this chunk is responsible for
+    std::vector<size_t> ids;      // frames held in `pixels`, in order; ids[0] is the previous readable frame
+    std::vector<char> missing;    // per frame of [first, last)
+    uint8_t* pixels = nullptr;    // pinned, (batch + 1) frames
+    std::vector<int32_t> nkp, nmatch, pairs;
+    std::vector<float> kp;
+    double decode_s = 0;
+};
+
+}  // namespace
+
+// VisualOdometry.cpp:38-193
+void VisualOdometry::run(const std::string image_dir, const size_t num_images, const std::string pose_file,
+                         const std::string output_csv) {
+    const double t_run = now_s();
+    stats = RunStats();
+    estimated_poses_.clear();
+    std::vector<Mat4> gt_poses;
+    if (!readGTFile(pose_file, gt_poses)) {
+        std::fprintf(stderr, "Failed to open pose file.\n");
+        return;
+    }
+    Mat4 T_curr = Mat4::identity();
+    estimated_poses_.push_back(T_curr);
+    std::string err;
+    const GrayImage first = readGray(frameFileName(image_dir, 0), &err);
+    if (first.empty()) {
+        std::fprintf(stderr, "Failed to load image: %s (%s)\n", frameFileName(image_dir, 0).c_str(), err.c_str());
+        return;
+    }
+    const int rows = first.rows, cols = first.cols;
+    ensure_ctx(rows, cols);
+    const size_t fbytes = static_cast<size_t>(rows) * cols;
+    const int maxkp = params.max_keypoints;
+    const size_t nchunks = num_images > 1 ? (num_images - 1 + batch - 1) / batch : 0;
+
+    Chunk chunks[3];
+    for (Chunk& c : chunks) {
+        c.pixels = static_cast<uint8_t*>(vo_host_alloc(fbytes * (batch + 1)));
+        if (!c.pixels) throw std::runtime_error("vo_host_alloc failed");
+    }
+    std::vector<uint8_t> anchor(fbytes);  // pixels of the query frame while a failure streak lasts
+    size_t anchor_id = static_cast<size_t>(-1);
+
+    // ---- stage 1: decode chunk k (frames 1 + k*batch ...), prefixed with the last readable frame before it
+    auto decode = [&](size_t k) {
+        const double t0 = now_s();
+        Chunk& c = chunks[k % 3];
+        c.first = 1 + k * batch;
+        c.last = std::min(num_images, c.first + batch);
+        const size_t cnt = c.last - c.first;
+        c.ids.clear();
+        c.missing.assign(cnt, 0);
+        if (k == 0) {
+            std::memcpy(c.pixels, first.data.data(), fbytes);
+            c.ids.push_back(0);
+        } else {
+            const Chunk& p = chunks[(k - 1) % 3];
+            std::memcpy(c.pixels, p.pixels + (p.ids.size() - 1) * fbytes, fbytes);
+            c.ids.push_back(p.ids.back());
+        }
+        // decode into per-frame scratch positions, then compact over missing frames
+        std::vector<char> ok(cnt, 0);
+        parallel_for(cnt, number_of_threads_, [&](size_t j) {
+            const GrayImage g = readGray(frameFileName(image_dir, c.first + j));
+            if (!g.empty() && g.rows == rows && g.cols == cols) {
+                std::memcpy(c.pixels + (1 + j) * fbytes, g.data.data(), fbytes);
+                ok[j] = 1;
+            }
+        });
+        size_t w = 1;
+        for (size_t j = 0; j < cnt; ++j) {
+            if (!ok[j]) { c.missing[j] = 1; continue; }
+            if (w != 1 + j) std::memmove(c.pixels + w * fbytes, c.pixels + (1 + j) * fbytes, fbytes);
+            c.ids.push_back(c.first + j);
+            ++w;
+        }
+        c.decode_s = now_s() - t0;
+    };
+
+    // ---- stage 2: the GPU front end on every frame of the chunk, consecutive pairs matched
+    auto frontend = [&](Chunk& c) {
+        const int n = static_cast<int>(c.ids.size());
+        c.nkp.assign(n, 0);
+        c.nmatch.assign(n > 1 ? n - 1 : 0, 0);
+        c.kp.resize(static_cast<size_t>(n) * maxkp * 2);
+        c.pairs.resize(static_cast<size_t>(n > 1 ? n - 1 : 0) * maxkp * 2);
+        if (n < 2) return;
+        const double t0 = now_s();
+        vo_seq_result out{c.nkp.data(), c.kp.data(), c.nmatch.data(), c.pairs.data()};
+        check(ctx_, vo_sequence_run(ctx_, c.pixels, n, rows, cols, static_cast<size_t>(cols), fbytes, &params, batch + 1, &out),
+              "vo_sequence_run");
+        stats.frontend_s += now_s() - t0;
+    };
+
+    // ---- stage 3: RANSAC + pose for every speculative pair (ids[j-1], ids[j]) of the chunk
+    std::vector<PairResult> results[3];
+    auto host_stage = [&](size_t k) {
+        const double t0 = now_s();
+        Chunk& c = chunks[k % 3];
+        std::vector<PairResult>& res = results[k % 3];
+        const size_t np = c.ids.size() > 1 ? c.ids.size() - 1 : 0;
+        res.assign(np, PairResult());
+        parallel_for(np, number_of_threads_, [&](size_t j) {
+            solve_pair(&c.kp[j * maxkp * 2], &c.kp[(j + 1) * maxkp * 2], &c.pairs[j * maxkp * 2], c.nmatch[j], c.ids[j + 1], res[j]);
+        });
+        return now_s() - t0;
+    };
+
+    // ---- stage 4: sequential composition with the reference's skip rules
+    size_t last_valid = 0;
+    double sum_kp = 0, sum_m = 0, sum_inl = 0;
+    size_t n_kp = 0, n_m = 0;
+    bool warned_gt = false;
+    std::vector<float> kpa(static_cast<size_t>(maxkp) * 2), kpb(static_cast<size_t>(maxkp) * 2);
+    std::vector<int32_t> prs(static_cast<size_t>(maxkp) * 2);
+    auto compose = [&](size_t k) {
+        const double t0 = now_s();
+        Chunk& c = chunks[k % 3];
+        const std::vector<PairResult>& res = results[k % 3];
+        size_t j = 0;  // position in ids of the last readable frame seen
+        for (size_t i = c.first; i < c.last; ++i) {
+            if (c.missing[i - c.first]) {  // VisualOdometry.cpp:78-83: pose repeated without the flip
+                std::fprintf(stderr, "Failed to load image: %s\n", frameFileName(image_dir, i).c_str());
+                estimated_poses_.push_back(T_curr);
+                ++stats.missing_frames;
+                continue;
+            }
+            ++j;
+            PairResult r;
+            if (last_valid == c.ids[j - 1]) {
+                r = res[j - 1];
+                sum_kp += c.nkp[j]; ++n_kp;
+            } else {  // the speculative pair started from a frame that failed: redo (last valid frame, i)
+                ++stats.respeculated;
+                const int sa = 2 * (batch + 1), sb = sa + 1;
+                int na = 0, nb = 0, nm = 0;
+                check(ctx_, vo_extract(ctx_, anchor.data(), rows, cols, static_cast<size_t>(cols), &params, sa), "vo_extract");
+                check(ctx_, vo_extract(ctx_, c.pixels + j * fbytes, rows, cols, static_cast<size_t>(cols), &params, sb), "vo_extract");
+                check(ctx_, vo_frame_fetch(ctx_, sa, &na, kpa.data(), nullptr, nullptr), "vo_frame_fetch");
+                check(ctx_, vo_frame_fetch(ctx_, sb, &nb, kpb.data(), nullptr, nullptr), "vo_frame_fetch");
+                check(ctx_, vo_match(ctx_, sa, sb, params.ratio, params.match_bits, prs.data(), maxkp, &nm), "vo_match");
+                solve_pair(kpa.data(), kpb.data(), prs.data(), nm, i, r);
+            }
+            stats.ransac_iterations += r.iterations;
+            sum_m += r.n_matches; ++n_m;
+            if (r.status != PairResult::OK) {
+                if (r.status == PairResult::FEW_MATCHES && verbose) std::fprintf(stderr, "Too few matches at frame %zu\n", i);
+                if (anchor_id != last_valid) {  // keep the query frame's pixels for the pairs to come
+                    if (last_valid == c.ids[j - 1]) std::memcpy(anchor.data(), c.pixels + (j - 1) * fbytes, fbytes);
+                    anchor_id = last_valid;
+                }
+                estimated_poses_.push_back(mul(flipZ, T_curr));
+                ++stats.skipped_frames;
+                continue;
+            }
+            sum_inl += r.n_inliers;
+            double gt_scale = 1.0;
+            if (i < gt_poses.size() && last_valid < gt_poses.size()) {
+                const Mat4 rel = mul(inverse_affine(gt_poses[i]), gt_poses[last_valid]);
+                gt_scale = std::sqrt(rel(0, 3) * rel(0, 3) + rel(1, 3) * rel(1, 3) + rel(2, 3) * rel(2, 3));
+            } else if (!warned_gt) {
+                std::fprintf(stderr, "Pose file has fewer lines than frames: unit step length used from frame %zu\n", i);
+                warned_gt = true;
+            }
+            last_valid = i;
+            Mat4 T_rel = Mat4::identity();
+            for (int a = 0; a < 3; ++a) {
+                for (int b = 0; b < 3; ++b) T_rel(a, b) = r.R(a, b);
+                T_rel(a, 3) = r.t(a) * gt_scale;
+            }
+            T_curr = mul(T_curr, T_rel);
+            estimated_poses_.push_back(mul(flipZ, T_curr));
+            ++stats.pairs_ok;
+        }
+        stats.compose_s += now_s() - t0;
+    };
+
+    try {
+        std::future<void> fut_dec;
+        std::future<double> fut_host;
+        if (nchunks) fut_dec = std::async(std::launch::async, decode, size_t(0));
+        for (size_t k = 0; k < nchunks; ++k) {
+            fut_dec.get();
+            stats.decode_s += chunks[k % 3].decode_s;
+            if (k + 1 < nchunks) fut_dec = std::async(std::launch::async, decode, k + 1);
+            frontend(chunks[k % 3]);
+            if (k > 0) { stats.host_s += fut_host.get(); }
+            fut_host = std::async(std::launch::async, host_stage, k);
+            if (k > 0) compose(k - 1);
+        }
+        if (nchunks) { stats.host_s += fut_host.get(); compose(nchunks - 1); }
+    } catch (...) {
+        for (Chunk& c : chunks) vo_host_free(c.pixels);
+        throw;
+    }
+    for (Chunk& c : chunks) vo_host_free(c.pixels);
+
+    if (!writePoseCSV(output_csv, estimated_poses_)) std::fprintf(stderr, "Failed to open output CSV file.\n");
+    else if (verbose) std::printf("Wrote estimated poses to: %s\n", output_csv.c_str());
+    stats.frames = num_images;
+    stats.mean_keypoints = n_kp ? sum_kp / n_kp : 0;
+    stats.mean_matches = n_m ? sum_m / n_m : 0;
+    stats.mean_inliers = stats.pairs_ok ? sum_inl / stats.pairs_ok : 0;
+    stats.wall_s = now_s() - t_run;
+}
+
+}  // namespace vo

@@ -1,0 +1,161 @@
+// vo_pose.cpp — see vo_pose.hpp.
+#include "vo_pose.hpp"
+
+#include <cmath>
+#include <cstdio>
+#include <fstream>
+#include <iomanip>
+#include <sstream>
+#include <stdexcept>
+
+namespace vo {
+
+const Mat4 flipZ{{1, 0, 0, 0, 0, 1, 0, 0, 0, 0, -1, 0, 0, 0, 0, 1}};
+
+// PoseUpdate.cpp:14-33
+Vec3 rotationMatrixToEulerAngles(const Mat3& R) {
+    const double sy = std::sqrt(R(0, 0) * R(0, 0) + R(1, 0) * R(1, 0));
+    const bool singular = sy < 1e-6;
+    double x, y, z;
+    if (!singular) {
+        x = std::atan2(R(2, 1), R(2, 2));
+        y = std::atan2(-R(2, 0), sy);
+        z = std::atan2(R(1, 0), R(0, 0));
+    } else {
+        x = std::atan2(-R(1, 2), R(1, 1));
+        y = std::atan2(-R(2, 0), sy);
+        z = 0;
+    }
+    return Vec3{{x, y, z}};
+}
+
+// PoseUpdate.cpp:35-42
+Mat3 quat_to_rot(double w, double x, double y, double z) {
+    return Mat3{{1 - 2 * y * y - 2 * z * z, 2 * x * y - 2 * z * w, 2 * x * z + 2 * y * w,
+                 2 * x * y + 2 * z * w, 1 - 2 * x * x - 2 * z * z, 2 * y * z - 2 * x * w,
+                 2 * x * z - 2 * y * w, 2 * y * z + 2 * x * w, 1 - 2 * x * x - 2 * y * y}};
+}
+
+// PoseUpdate.cpp:43-50
+Mat4 readGTLine(const std::string& line) {
+    std::stringstream ss(line);
+    Mat4 T = Mat4::identity();
+    for (int i = 0; i < 12; ++i) {
+        double v;
+        if (!(ss >> v)) break;  // operator>> leaves the target at 0 on failure in C++11; a short line is malformed either way
+        T(i / 4, i % 4) = v;
+    }
+    return T;
+}
+
+bool readGTFile(const std::string& path, std::vector<Mat4>& poses) {
+    std::ifstream in(path);
+    if (!in.is_open()) return false;
+    std::string line;
+    while (std::getline(in, line)) poses.push_back(readGTLine(line));
+    return true;
+}
+
+// PoseUpdate.cpp:52-69
+std::string formatPoseCSVLine(const Mat4& T) {
+    std::ostringstream os;
+    for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 4; ++c) {
+            os << std::setprecision(9) << T(r, c);
+            if (!(r == 2 && c == 3)) os << ",";
+        }
+    os << "\n";
+    return os.str();
+}
+
+bool writePoseCSV(const std::string& filename, const std::vector<Mat4>& poses) {
+    std::ofstream file(filename);
+    if (!file.is_open()) return false;
+    for (const Mat4& T : poses) file << formatPoseCSVLine(T);
+    return static_cast<bool>(file);
+}
+
+std::string frameFileName(const std::string& image_dir, size_t index) {
+    char name[32];
+    std::snprintf(name, sizeof(name), "%06zu.png", index);
+    return image_dir + name;
+}
+
+void triangulatePoint(const Mat3& R, const Vec3& t, double x1, double y1, double x2, double y2, double X[4]) {
+    // P1 = [I | 0], P2 = [R | t]; rows x*P[2] - P[0], y*P[2] - P[1] for both views
+    double A[16];
+    const double P1[3][4] = {{1, 0, 0, 0}, {0, 1, 0, 0}, {0, 0, 1, 0}};
+    double P2[3][4];
+    for (int i = 0; i < 3; ++i) { for (int j = 0; j < 3; ++j) P2[i][j] = R(i, j); P2[i][3] = t(i); }
+    for (int j = 0; j < 4; ++j) {
+        A[0 * 4 + j] = x1 * P1[2][j] - P1[0][j];
+        A[1 * 4 + j] = y1 * P1[2][j] - P1[1][j];
+        A[2 * 4 + j] = x2 * P2[2][j] - P2[0][j];
+        A[3 * 4 + j] = y2 * P2[2][j] - P2[1][j];
+    }
+    double s[4], V[16];
+    jacobi_svd(A, 4, 4, s, V);
+    for (int i = 0; i < 4; ++i) X[i] = V[i * 4 + 3];
+}
+
+// PoseUpdate.hpp:61-179
+PoseResult PoseUpdate::getPoseEx(const Mat3& F, const std::vector<Point2f>& points1, const std::vector<Point2f>& points2,
+                                 double GT_pos_norm) const {
+    Mat3 E = mul(mul(transpose(K), F), K);
+    const double en = frobenius(E);
+    E = scaled(E, 1.0 / en);
+    int nonzero = 0;
+    for (double v : E.m) nonzero += v != 0.0;  // cv::countNonZero: NaN counts as non-zero
+    if (nonzero < 5) throw std::runtime_error("Degenerate essential matrix");
+
+    Mat3 U, V;
+    Vec3 S;
+    svd3(E, U, S, V);
+    Mat3 Vt = transpose(V);
+    if (det(U) < 0) U = scaled(U, -1.0);
+    if (det(Vt) < 0) Vt = scaled(Vt, -1.0);
+    const Mat3 W{{0, -1, 0, 1, 0, 0, 0, 0, 1}};
+    Mat3 R1 = mul(mul(U, W), Vt);
+    Mat3 R2 = mul(mul(U, transpose(W)), Vt);
+    if (det(R1) < 0) R1 = scaled(R1, -1.0);
+    if (det(R2) < 0) R2 = scaled(R2, -1.0);
+    const Vec3 t{{U(0, 2), U(1, 2), U(2, 2)}};
+    const Vec3 tn{{-t(0), -t(1), -t(2)}};
+    const Mat3* Rs[4] = {&R1, &R1, &R2, &R2};
+    const Vec3* ts[4] = {&t, &tn, &t, &tn};
+
+    // cv::undistortPoints(points, K, no distortion): (x - cx) / fx, (y - cy) / fy, stored as float
+    const size_t n = std::min(points1.size(), points2.size());
+    std::vector<Point2f> n1(n), n2(n);
+    for (size_t i = 0; i < n; ++i) {
+        n1[i] = Point2f{static_cast<float>((points1[i].x - K(0, 2)) / K(0, 0)), static_cast<float>((points1[i].y - K(1, 2)) / K(1, 1))};
+        n2[i] = Point2f{static_cast<float>((points2[i].x - K(0, 2)) / K(0, 0)), static_cast<float>((points2[i].y - K(1, 2)) / K(1, 1))};
+    }
+
+    PoseResult best;
+    for (int c = 0; c < 4; ++c) {
+        const Mat3& R = *Rs[c];
+        const Vec3& tc = *ts[c];
+        int positive = 0;
+        for (size_t i = 0; i < n; ++i) {
+            double X[4];
+            triangulatePoint(R, tc, n1[i].x, n1[i].y, n2[i].x, n2[i].y, X);
+            for (double& v : X) v = static_cast<double>(static_cast<float>(v));  // triangulatePoints returns CV_32F for float input
+            const double w = X[3];
+            if (std::fabs(w) < 1e-6) continue;
+            const Vec3 P{{X[0] / w, X[1] / w, X[2] / w}};
+            const double z1 = P(2);
+            const Vec3 P2 = mul(R, P);
+            const double z2 = P2(2) + tc(2);
+            if (z1 > 0 && z2 > 0) ++positive;
+        }
+        if (positive > best.positive_depth) { best.positive_depth = positive; best.R = R; best.t = tc; best.candidate = c; }
+    }
+    if (det(best.R) < 0) best.R = scaled(best.R, -1.0);
+    const double tnorm = norm(best.t);
+    if (tnorm > 1e-6)
+        for (int i = 0; i < 3; ++i) best.t(i) *= GT_pos_norm / tnorm;
+    return best;
+}
+
+}  // namespace vo

@@ -1,0 +1,137 @@
+// vo_ransac.cpp — see vo_ransac.hpp.  Follows /root/reference/ransac.cpp stage by stage (line references
+// at each function); written against vo_linalg.hpp instead of Eigen.
+#include "vo_ransac.hpp"
+
+#include <algorithm>
+#include <cmath>
+#include <iterator>
+#include <limits>
+#include <random>
+
+namespace vo {
+
+// ransac.cpp:12-23: (x'^T F x)^2 / ((Fx)_0^2 + (Fx)_1^2 + (F^T x')_0^2 + (F^T x')_1^2)
+double computeSampsonError(const Mat3& F, const Vec3& x, const Vec3& xp) {
+    const Vec3 Fx = mul(F, x);
+    const Vec3 Ftx = mul(transpose(F), xp);
+    const double e = dot(xp, Fx);
+    const double numerator = e * e;
+    const double denominator = Fx(0) * Fx(0) + Fx(1) * Fx(1) + Ftx(0) * Ftx(0) + Ftx(1) * Ftx(1);
+    if (denominator < 1e-12) return std::numeric_limits<double>::max();
+    return numerator / denominator;
+}
+
+// ransac.cpp:25-61: Hartley normalisation, centroid to the origin and RMS distance sqrt(2)
+void FundamentalMatrix::normalizePoints(const std::vector<PointPair>& points, std::vector<Vec3>& n1,
+                                        std::vector<Vec3>& n2, Mat3& T1, Mat3& T2) {
+    double mx1 = 0, my1 = 0, mx2 = 0, my2 = 0;
+    for (const auto& p : points) { mx1 += p.first.x; my1 += p.first.y; mx2 += p.second.x; my2 += p.second.y; }
+    const double n = static_cast<double>(points.size());
+    mx1 /= n; my1 /= n; mx2 /= n; my2 /= n;
+    double s1 = 0, s2 = 0;
+    for (const auto& p : points) {
+        s1 += (p.first.x - mx1) * (p.first.x - mx1) + (p.first.y - my1) * (p.first.y - my1);
+        s2 += (p.second.x - mx2) * (p.second.x - mx2) + (p.second.y - my2) * (p.second.y - my2);
+    }
+    s1 = std::sqrt(2.0) / std::sqrt(s1 / n);
+    s2 = std::sqrt(2.0) / std::sqrt(s2 / n);
+    T1 = Mat3::zero(); T2 = Mat3::zero();
+    T1(0, 0) = s1; T1(0, 2) = -s1 * mx1; T1(1, 1) = s1; T1(1, 2) = -s1 * my1; T1(2, 2) = 1;
+    T2(0, 0) = s2; T2(0, 2) = -s2 * mx2; T2(1, 1) = s2; T2(1, 2) = -s2 * my2; T2(2, 2) = 1;
+    n1.clear(); n2.clear();
+    n1.reserve(points.size()); n2.reserve(points.size());
+    for (const auto& p : points) {
+        n1.push_back(mul(T1, Vec3{{p.first.x, p.first.y, 1.0}}));
+        n2.push_back(mul(T2, Vec3{{p.second.x, p.second.y, 1.0}}));
+    }
+}
+
+// ransac.cpp:63-93.  Note the reference's row layout (p1.x*p2.x, p1.x*p2.y, p1.x, ...): with f reshaped
+// row-major it encodes p1^T F p2 = 0, and F is then de-normalised as T2^T F T1 - kept as written.
+Mat3 FundamentalMatrix::computeFundamentalMatrix(const std::vector<PointPair>& points) {
+    Mat3 T1, T2;
+    std::vector<Vec3> n1, n2;
+    normalizePoints(points, n1, n2, T1, T2);
+    const int m = static_cast<int>(points.size());
+    std::vector<double> A(static_cast<size_t>(m) * 9);
+    for (int i = 0; i < m; ++i) {
+        const Vec3 &p1 = n1[i], &p2 = n2[i];
+        double* r = &A[static_cast<size_t>(i) * 9];
+        r[0] = p1(0) * p2(0); r[1] = p1(0) * p2(1); r[2] = p1(0);
+        r[3] = p1(1) * p2(0); r[4] = p1(1) * p2(1); r[5] = p1(1);
+        r[6] = p2(0);         r[7] = p2(1);         r[8] = 1.0;
+    }
+    double s[9], V[81];
+    jacobi_svd(A.data(), m, 9, s, V);
+    Mat3 F;
+    for (int i = 0; i < 9; ++i) F.m[i] = V[i * 9 + 8];  // right singular vector of the smallest singular value
+    F = mul(mul(transpose(T2), F), T1);
+    // rank 2: zero the smallest singular value
+    Mat3 U, W;
+    Vec3 sv;
+    svd3(F, U, sv, W);
+    Mat3 D = Mat3::zero();
+    D(0, 0) = sv(0); D(1, 1) = sv(1);
+    return mul(mul(U, D), transpose(W));
+}
+
+void FundamentalMatrix::fit(const std::vector<PointPair>& sample) {
+    if (sample.size() < 8) return;
+    F = computeFundamentalMatrix(sample);
+    inliers = sample;
+}
+
+int FundamentalMatrix::countInliers(const std::vector<PointPair>& data, double threshold) const {
+    int count = 0;
+    for (const auto& pr : data) {
+        const Vec3 p1{{pr.first.x, pr.first.y, 1.0}}, p2{{pr.second.x, pr.second.y, 1.0}};
+        count += std::fabs(dot(p2, mul(F, p1))) < threshold;
+    }
+    return count;
+}
+
+RansacStats Ransac::run(FundamentalMatrix& model, const std::vector<PointPair>& data, double probability,
+                        double sampsonThreshold, int numThreads, std::uint64_t seed) const {
+    RansacStats st;
+    const int N = static_cast<int>(data.size());
+    const int sampleSize = 8;
+    double outlierRatio = 0.5;
+    int maxIterations = static_cast<int>(std::log(1.0 - probability) / std::log(1.0 - std::pow(1.0 - outlierRatio, sampleSize)));
+    int bestInliers = 0;
+    std::vector<PointPair> bestInlierSet;
+    std::mt19937 rng(seed ? static_cast<std::mt19937::result_type>(seed) : std::random_device{}());
+    if (numThreads < 1) numThreads = 1;
+    // the reference scores chunks [t*chunk, min(N, (t+1)*chunk)), t < numThreads: the tail N % numThreads is never scored
+    const int chunkSize = N / numThreads;
+    const int scored = std::min(N, numThreads * chunkSize);
+    std::vector<PointPair> sample, currentInliers;
+    for (int iter = 0; iter < maxIterations; ++iter) {
+        ++st.iterations;
+        sample.clear();
+        std::sample(data.begin(), data.end(), std::back_inserter(sample), sampleSize, rng);
+        FundamentalMatrix tempModel;
+        tempModel.fit(sample);  // fewer than 8 correspondences: F stays zero, every Sampson error is "max"
+        const Mat3 F = tempModel.getMatrix();
+        currentInliers.clear();
+        for (int i = 0; i < scored; ++i) {
+            const Vec3 x{{data[i].first.x, data[i].first.y, 1.0}}, xp{{data[i].second.x, data[i].second.y, 1.0}};
+            if (computeSampsonError(F, x, xp) < sampsonThreshold) currentInliers.push_back(data[i]);
+        }
+        if (static_cast<int>(currentInliers.size()) > bestInliers) {
+            bestInliers = static_cast<int>(currentInliers.size());
+            bestInlierSet = currentInliers;
+            outlierRatio = 1.0 - static_cast<double>(bestInliers) / N;
+            const double denom = std::log(1.0 - std::pow(1.0 - outlierRatio, sampleSize));
+            if (denom != 0.0) {
+                // log(1-p)/denom can be +-inf (all inliers: denom = -inf gives 0, fine) or huge: clamp in double first
+                const double it = std::log(1.0 - probability) / denom;
+                maxIterations = it >= 2000.0 ? 2000 : (it <= 100.0 ? 100 : static_cast<int>(it));
+            }
+        }
+    }
+    st.best_inliers = bestInliers;
+    model.fit(bestInlierSet);
+    return st;
+}
+
+}  // namespace vo
