@@ -90,31 +90,75 @@ inline Mat4 inverse_affine(const Mat4& a) {
 // One-sided (Hestenes) Jacobi SVD of a row-major m x n matrix, any m >= 1, n <= 16.
 //   A = U diag(s) V^T, singular values sorted in descending order.
 // Outputs: s[n], V (n x n, row-major, columns = right singular vectors), and, if `Uout` is given, the
-// n columns A v_i / s_i (m x n, row-major; columns with s_i == 0 are left as zero).
+// n columns A v_i / s_i (m x n, row-major; columns with s_i == 0 are left as zero; only for m <= n... see below).
+// Tall matrices (m > n, the final fit over hundreds of inliers) are first reduced to their n x n triangular
+// factor with Householder reflections - the same preconditioning Eigen::JacobiSVD applies - so the sweeps cost
+// O(n^3) instead of O(m n^2); R has the singular values and right singular vectors of A.  Uout is not
+// available for m > n (never needed here).
 // The null vector the 8-point algorithm needs is column n-1 of V (also when m < n: the working columns
 // live in R^m, so at least n - m of them converge to zero).
 inline void jacobi_svd(const double* A, int m, int n, double* s, double* V, double* Uout = nullptr) {
-    std::vector<double> W(A, A + (size_t)m * n);  // working copy; columns converge to u_i * s_i
+    std::vector<double> Wheap;
+    double Wstack[16 * 16];
+    double* W;
+    int rows = m;
+    if (m > n) {
+        // Householder QR in place on a copy; keep R (upper triangle) as the n x n working matrix
+        Wheap.assign(A, A + (size_t)m * n);
+        double* Q = Wheap.data();
+        for (int k = 0; k < n; ++k) {
+            double nrm2 = 0;
+            for (int i = k; i < m; ++i) nrm2 += Q[(size_t)i * n + k] * Q[(size_t)i * n + k];
+            const double nrm = std::sqrt(nrm2);
+            if (nrm == 0.0) continue;
+            const double akk = Q[(size_t)k * n + k];
+            const double alpha = akk > 0 ? -nrm : nrm;
+            // v = x - alpha e1 (stored in column k below the diagonal, v_k separately), H = I - 2 v v^T / (v^T v)
+            const double vk = akk - alpha;
+            const double vtv = nrm2 - akk * akk + vk * vk;
+            if (vtv == 0.0) continue;
+            for (int j = k + 1; j < n; ++j) {
+                double d = vk * Q[(size_t)k * n + j];
+                for (int i = k + 1; i < m; ++i) d += Q[(size_t)i * n + k] * Q[(size_t)i * n + j];
+                const double f = 2.0 * d / vtv;
+                Q[(size_t)k * n + j] -= f * vk;
+                for (int i = k + 1; i < m; ++i) Q[(size_t)i * n + j] -= f * Q[(size_t)i * n + k];
+            }
+            Q[(size_t)k * n + k] = alpha;
+            for (int i = k + 1; i < m; ++i) Q[(size_t)i * n + k] = 0.0;  // only for clarity: rows >= n are dropped below
+        }
+        W = Wstack;
+        for (int i = 0; i < n; ++i)
+            for (int j = 0; j < n; ++j) W[i * n + j] = j >= i ? Q[(size_t)i * n + j] : 0.0;
+        rows = n;
+        Uout = nullptr;
+    } else {
+        W = Wstack;
+        std::copy(A, A + (size_t)m * n, W);  // m <= n <= 16
+    }
     for (int i = 0; i < n; ++i) for (int j = 0; j < n; ++j) V[i * n + j] = i == j ? 1.0 : 0.0;
     const double eps = 1e-15;
+    double scale2 = 0;  // squared Frobenius norm: columns below 1e-30 of it are numerically zero
+    for (int i = 0; i < rows * n; ++i) scale2 += W[i] * W[i];
+    const double zero2 = scale2 * 1e-60;
     for (int sweep = 0; sweep < 60; ++sweep) {
         bool rotated = false;
         for (int p = 0; p < n - 1; ++p)
             for (int q = p + 1; q < n; ++q) {
                 double alpha = 0, beta = 0, gamma = 0;
-                for (int i = 0; i < m; ++i) {
-                    const double wp = W[(size_t)i * n + p], wq = W[(size_t)i * n + q];
+                for (int i = 0; i < rows; ++i) {
+                    const double wp = W[i * n + p], wq = W[i * n + q];
                     alpha += wp * wp; beta += wq * wq; gamma += wp * wq;
                 }
-                if (gamma == 0.0 || std::fabs(gamma) <= eps * std::sqrt(alpha * beta)) continue;
+                if (gamma == 0.0 || alpha <= zero2 || beta <= zero2 || std::fabs(gamma) <= eps * std::sqrt(alpha * beta)) continue;
                 rotated = true;
                 const double zeta = (beta - alpha) / (2.0 * gamma);
                 const double t = (zeta >= 0 ? 1.0 : -1.0) / (std::fabs(zeta) + std::sqrt(1.0 + zeta * zeta));
                 const double c = 1.0 / std::sqrt(1.0 + t * t), sn = c * t;
-                for (int i = 0; i < m; ++i) {
-                    const double wp = W[(size_t)i * n + p], wq = W[(size_t)i * n + q];
-                    W[(size_t)i * n + p] = c * wp - sn * wq;
-                    W[(size_t)i * n + q] = sn * wp + c * wq;
+                for (int i = 0; i < rows; ++i) {
+                    const double wp = W[i * n + p], wq = W[i * n + q];
+                    W[i * n + p] = c * wp - sn * wq;
+                    W[i * n + q] = sn * wp + c * wq;
                 }
                 for (int i = 0; i < n; ++i) {
                     const double vp = V[i * n + p], vq = V[i * n + q];
@@ -128,19 +172,19 @@ inline void jacobi_svd(const double* A, int m, int n, double* s, double* V, doub
     std::array<int, 16> order{};
     for (int j = 0; j < n; ++j) {
         double a = 0;
-        for (int i = 0; i < m; ++i) a += W[(size_t)i * n + j] * W[(size_t)i * n + j];
+        for (int i = 0; i < rows; ++i) a += W[i * n + j] * W[i * n + j];
         nrm[j] = std::sqrt(a); order[j] = j;
     }
     std::stable_sort(order.begin(), order.begin() + n, [&](int a, int b) { return nrm[a] > nrm[b]; });
-    std::vector<double> Vs((size_t)n * n);
+    double Vs[16 * 16];
     for (int j = 0; j < n; ++j) {
         s[j] = nrm[order[j]];
-        for (int i = 0; i < n; ++i) Vs[(size_t)i * n + j] = V[i * n + order[j]];
+        for (int i = 0; i < n; ++i) Vs[i * n + j] = V[i * n + order[j]];
     }
-    std::copy(Vs.begin(), Vs.end(), V);
+    std::copy(Vs, Vs + n * n, V);
     if (Uout)
         for (int j = 0; j < n; ++j)
-            for (int i = 0; i < m; ++i) Uout[(size_t)i * n + j] = s[j] > 0 ? W[(size_t)i * n + order[j]] / s[j] : 0.0;
+            for (int i = 0; i < rows; ++i) Uout[(size_t)i * n + j] = s[j] > 0 ? W[i * n + order[j]] / s[j] : 0.0;
 }
 
 // Full SVD of a 3x3 matrix: A = U diag(s) V^T with orthogonal U and V (columns of U for vanishing singular

@@ -113,9 +113,15 @@ RansacStats Ransac::run(FundamentalMatrix& model, const std::vector<PointPair>& 
         tempModel.fit(sample);  // fewer than 8 correspondences: F stays zero, every Sampson error is "max"
         const Mat3 F = tempModel.getMatrix();
         currentInliers.clear();
-        for (int i = 0; i < scored; ++i) {
-            const Vec3 x{{data[i].first.x, data[i].first.y, 1.0}}, xp{{data[i].second.x, data[i].second.y, 1.0}};
-            if (computeSampsonError(F, x, xp) < sampsonThreshold) currentInliers.push_back(data[i]);
+        for (int i = 0; i < scored; ++i) {  // computeSampsonError inlined (same operations in the same order)
+            const double x0 = data[i].first.x, x1 = data[i].first.y, p0 = data[i].second.x, p1 = data[i].second.y;
+            const double Fx0 = F(0, 0) * x0 + F(0, 1) * x1 + F(0, 2) * 1.0, Fx1 = F(1, 0) * x0 + F(1, 1) * x1 + F(1, 2) * 1.0,
+                         Fx2 = F(2, 0) * x0 + F(2, 1) * x1 + F(2, 2) * 1.0;
+            const double Ft0 = F(0, 0) * p0 + F(1, 0) * p1 + F(2, 0) * 1.0, Ft1 = F(0, 1) * p0 + F(1, 1) * p1 + F(2, 1) * 1.0;
+            const double e = p0 * Fx0 + p1 * Fx1 + 1.0 * Fx2;
+            const double den = Fx0 * Fx0 + Fx1 * Fx1 + Ft0 * Ft0 + Ft1 * Ft1;
+            if (den < 1e-12) continue;  // error = max
+            if (e * e / den < sampsonThreshold) currentInliers.push_back(data[i]);
         }
         if (static_cast<int>(currentInliers.size()) > bestInliers) {
             bestInliers = static_cast<int>(currentInliers.size());
