@@ -39,6 +39,8 @@
 // result (exact products by 0.5 / 4, sums, the sqrt refinement's intended FMAs).
 #include <cuda_fp16.h>
 
+#include <type_traits>
+
 #include "vo_internal.cuh"
 
 namespace {
@@ -83,34 +85,62 @@ __device__ __forceinline__ u64 shfl_dn2(u64 v) {
     float lo, hi; upk(v, lo, hi);
     return pk(__shfl_down_sync(FULL, lo, 1), __shfl_down_sync(FULL, hi, 1));
 }
+// Blackwell mixed-precision FMA (FHFMA): fp16 multiplicands taken from either half of a half2, fp32 addend and
+// result, ONE rounding to fp32.  The products here are squares of integers <= 2040 and the sums stay below
+// 2^24, so every result is exact; what it buys is the fp16 -> fp32 conversions and the operand packing.
+__device__ __forceinline__ float fhfma_lo(__half2 v, float c) {
+    float d; asm("{.reg .b16 l, h; mov.b32 {l, h}, %1; fma.rn.f32.f16 %0, l, l, %2;}" : "=f"(d) : "r"(h2u(v)), "f"(c)); return d;
+}
+__device__ __forceinline__ float fhfma_hi(__half2 v, float c) {
+    float d; asm("{.reg .b16 l, h; mov.b32 {l, h}, %1; fma.rn.f32.f16 %0, h, h, %2;}" : "=f"(d) : "r"(h2u(v)), "f"(c)); return d;
+}
+__device__ __forceinline__ float fhfnma_lo(__half2 v, float c) {  // c - v.lo^2
+    float d; asm("{.reg .b16 l, h, n; mov.b32 {l, h}, %1; neg.f16 n, l; fma.rn.f32.f16 %0, n, l, %2;}" : "=f"(d) : "r"(h2u(v)), "f"(c)); return d;
+}
+__device__ __forceinline__ float fhfnma_hi(__half2 v, float c) {  // c - v.hi^2
+    float d; asm("{.reg .b16 l, h, n; mov.b32 {l, h}, %1; neg.f16 n, h; fma.rn.f32.f16 %0, n, h, %2;}" : "=f"(d) : "r"(h2u(v)), "f"(c)); return d;
+}
 __device__ __forceinline__ float rsqrt_approx(float x) { float y; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 
-// Two pixels of R = tr/2 - 0.5*sqrt(tr^2 - 4 det), det = a*b - c*c  (corner_detection_parallel.cpp:93-98).
+// Four pixels of R = tr/2 - 0.5*sqrt(tr^2 - 4 det), det = a*b - c*c  (corner_detection_parallel.cpp:93-98).
 // Every operation rounds once to nearest like the reference's scalar code (its final subtraction in
-// double followed by narrowing equals one fp32 rounding: 53 >= 2*24+2).  disc is an integer-valued float,
-// so it is 0, <= -1 or >= 1.  sqrt: the correctly rounded fast path of sqrtf (rsqrt seed, one refinement),
-// valid for every disc >= 1 that can occur here (< 2^50); the seed is taken at max(disc, 1/4) so that
-// disc == 0 gives exactly 0, and disc < 0 (NaN in the reference -> comparison false -> 0) is selected after.
-__device__ __forceinline__ void shi_tomasi2(float a0, float b0, float c0, float a1, float b1, float c1, float thr,
-                                            float& r0, float& r1) {
-    const u64 ab = pk(__fmul_rn(a0, b0), __fmul_rn(a1, b1));
-    const u64 cc = pk(__fmul_rn(c0, c0), __fmul_rn(c1, c1));
-    const float t0 = __fadd_rn(a0, b0), t1 = __fadd_rn(a1, b1);  // exact (integers < 2^24)
-    const u64 tr = pk(t0, t1);
-    const u64 tt = pk(__fmul_rn(t0, t0), __fmul_rn(t1, t1));
-    const u64 det = sub2(ab, cc);
-    const u64 disc = sub2(tt, mul2(det, pk(4.f, 4.f)));  // 4*det is exact
-    float d0, d1; upk(disc, d0, d1);
-    const u64 y = pk(rsqrt_approx(fmaxf(d0, 0.25f)), rsqrt_approx(fmaxf(d1, 0.25f)));
-    const u64 half = pk(0.5f, 0.5f);
-    const u64 s = mul2(disc, y), h = mul2(y, half);
-    float s0, s1; upk(s, s0, s1);
-    const u64 e = fma2(pk(-s0, -s1), s, disc);
-    const u64 sq = fma2(e, h, s);
-    const u64 r = sub2(mul2(tr, half), mul2(half, sq));  // both products exact
-    float q0, q1; upk(r, q0, q1);
-    r0 = (d0 >= 0.0f && q0 > thr) ? q0 : 0.0f;
-    r1 = (d1 >= 0.0f && q1 > thr) ? q1 : 0.0f;
+// double followed by narrowing equals one fp32 rounding: 53 >= 2*24+2).  The three rounded products are
+// scalar (ptxas would contract a packed mul + add pair); the sums that follow them are FMAs by an exact
+// constant (x*(-1), x*4, x*0.5 are exact, so fma(x, k, y) rounds once, like the reference's add), which ptxas
+// cannot contract any further, and they run packed, two pixels per instruction.
+// Signs: the chain carries nd = -disc, ns = -s, ne = -e, nsq = -sqrt: round-to-nearest is sign-symmetric, so
+// each value is exactly the negative of the reference's and no negation is ever issued.
+// disc is an integer-valued float: 0, <= -1 or >= 1.  sqrt: the correctly rounded fast path of sqrtf (rsqrt
+// seed, one refinement), valid for every disc >= 1 that can occur here (< 2^50).  The seed is taken at
+// disc + 1e-30 (== disc for disc >= 1): disc == 0 gives exactly 0, and disc < 0 gives NaN, which fails the
+// threshold comparison exactly like the reference's NaN does.
+// Pixel order: A/B index k = pixel k; cE = (c0, c2), cO = (c1, c3) as fp16 (integers <= 2040, exact).
+__device__ __forceinline__ void shi_tomasi4(const float (&A)[4], const float (&B)[4], __half2 cE, __half2 cO, float thr,
+                                            float (&out)[4]) {
+    float cc[4], ab[4], t[4], ntt[4], dz[4];
+    cc[0] = fhfma_lo(cE, 0.f); cc[1] = fhfma_lo(cO, 0.f); cc[2] = fhfma_hi(cE, 0.f); cc[3] = fhfma_hi(cO, 0.f);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        ab[k] = __fmul_rn(A[k], B[k]);
+        t[k] = __fadd_rn(A[k], B[k]);  // exact (integers < 2^24)
+        ntt[k] = __fmul_rn(t[k], -t[k]);
+    }
+    const u64 m1 = pk(-1.f, -1.f), p4 = pk(4.f, 4.f), half = pk(0.5f, 0.5f);
+#pragma unroll
+    for (int q = 0; q < 4; q += 2) {
+        const u64 det = fma2(pk(cc[q], cc[q + 1]), m1, pk(ab[q], ab[q + 1]));
+        const u64 nd = fma2(det, p4, pk(ntt[q], ntt[q + 1]));  // -(tr^2 - 4 det)
+        float n0, n1; upk(nd, n0, n1);
+        dz[q] = __fsub_rn(1e-30f, n0); dz[q + 1] = __fsub_rn(1e-30f, n1);
+        const u64 y = pk(rsqrt_approx(dz[q]), rsqrt_approx(dz[q + 1]));
+        const u64 ns = mul2(nd, y), h = mul2(y, half);
+        const u64 ne = fma2(ns, ns, nd);
+        const u64 nsq = fma2(ne, h, ns);
+        const u64 r = fma2(nsq, half, mul2(pk(t[q], t[q + 1]), half));
+        float r0, r1; upk(r, r0, r1);
+        out[q] = r0 > thr ? r0 : 0.0f;
+        out[q + 1] = r1 > thr ? r1 : 0.0f;
+    }
 }
 
 // ---- per-lane history rings ------------------------------------------------------------------------------
@@ -219,7 +249,7 @@ k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows, float thr
         sts2(qa + 2048 + k * 256, make_uint2(0u, 0u)); sts2(qb + 2048 + k * 256, make_uint2(0u, 0u));
         sts4(ja + k * 512, make_uint4(0u, 0u, 0u, 0u)); sts4(jb + k * 512, make_uint4(0u, 0u, 0u, 0u));
     }
-    u64 sab[4] = {0ull, 0ull, 0ull, 0ull};  // running 5-row sums (sum Jx^2, sum Jy^2) per pixel
+    float sa[4] = {0.f, 0.f, 0.f, 0.f}, sb[4] = {0.f, 0.f, 0.f, 0.f};  // running 5-row sums of Jx^2, Jy^2 per pixel
 
     const __half2 hz = __floats2half2_rn(0.f, 0.f), two = __floats2half2_rn(2.f, 2.f), k1024 = __floats2half2_rn(1024.f, 1024.f);
 
@@ -234,8 +264,11 @@ k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows, float thr
     uint8_t* blur_p = FROM_BLURRED ? nullptr : blur_out + (long long)(r0 - 3) * blur_pitch + x;
     float* R_p = R + (long long)(r0 - 6) * R_pitch + x;
 
-#pragma unroll 1
-    for (int t0 = 0; t0 < T; t0 += RB) {
+    // One trip = four steps.  STEADY trips (all four blurred / gradient / response rows inside the segment and the
+    // image, a further trip to request) carry no row tests; the first four and the last one or two trips of a
+    // segment run the general form.
+    auto trip = [&](auto steady_tag, const int t0) {
+        constexpr bool STEADY = decltype(steady_tag)::value;
         // ---- 0. the four rows requested a trip ago; request the next four -----------------------------------
         uint32_t w[RB];
 #pragma unroll
@@ -245,7 +278,7 @@ k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows, float thr
             for (int j = 0; j < RB; ++j)
                 w[j] = __byte_perm(__shfl_sync(FULL, w[j], srcA), __shfl_sync(FULL, w[j], srcB), msel);
         }
-        if (t0 + RB < T) issue(r0 + t0 + RB + load_off);
+        if (STEADY || t0 + RB < T) issue(r0 + t0 + RB + load_off);
 
         // ---- 1. blurred rows r-3 for the four steps ----------------------------------------------------------
         // index i of the local windows = step offset c + 6, c in [-6, 3]
@@ -290,7 +323,7 @@ k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows, float thr
                 S3 = __dp2a_lo(RE_, 56u | (8u << 8), S3);  S3 = __dp2a_lo(RO_, 28u, S3);
                 const uint32_t hE = __byte_perm(S0, S2, 0x7632), hO = __byte_perm(S1, S3, 0x7632);  // fp16 1024 + B
                 const int rb = r0 + t0 + j - 3;
-                if (store_lane && rb >= ys && rb < ye)
+                if (store_lane && (STEADY || (rb >= ys && rb < ye)))
                     *reinterpret_cast<uint32_t*>(blur_p + j * blur_pitch) = __byte_perm(hE, hO, 0x6240);
                 bE[6 + j] = __hsub2(u2h(hE), k1024);
                 bO[6 + j] = __hsub2(u2h(hO), k1024);
@@ -305,13 +338,13 @@ k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows, float thr
                 sts2(slot_of(qa, qb, j, 256) + 2048, make_uint2(h2u(bE[6 + j]), h2u(bO[6 + j])));
             }
         }
-        if (t0 >= 8) {  // gradient rows g = r-4 < ys-2 never enter an output window
+        if (STEADY || t0 >= 8) {  // gradient rows g = r-4 < ys-2 never enter an output window
 #pragma unroll
             for (int j = 0; j < RB; ++j) {
                 // ---- 2. gradients of row g from blurred rows g-1, g, g+1 (steps t-2, t-1, t) -----------------
                 const int g = r0 + t0 + j - 4;
                 __half2 jxE = hz, jxO = hz, jyE = hz, jyO = hz;
-                if (g >= 1 && g <= H - 2) {  // warp-uniform; rows 0 and H-1 stay zero
+                if (STEADY || (g >= 1 && g <= H - 2)) {  // warp-uniform; rows 0 and H-1 stay zero
                     const __half2 pE = bE[4 + j], pO = bO[4 + j], cE = bE[5 + j], cO = bO[5 + j], nE = bE[6 + j], nO = bO[6 + j];
                     const __half2 dE = __hsub2(pE, nE), dO = __hsub2(pO, nO);                                      // [1,0,-1]^T
                     const __half2 sE = __hadd2(__hfma2(cE, two, pE), nE), sO = __hadd2(__hfma2(cO, two, pO), nO);  // [1,2,1]^T
@@ -331,32 +364,29 @@ k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows, float thr
                     const uint4 old = lds4(slot_of(ja, jb, j - 5, 512));  // row g-5 (written at step t-5)
                     sts4(slot_of(ja, jb, j, 512), make_uint4(h2u(jxE), h2u(jxO), h2u(jyE), h2u(jyO)));
                     const __half2 oxE = u2h(old.x), oxO = u2h(old.y), oyE = u2h(old.z), oyO = u2h(old.w);
-                    u64 n, o;
-                    n = pk(__low2float(jxE), __low2float(jyE));   sab[0] = fma2(n, n, sab[0]);
-                    o = pk(__low2float(oxE), __low2float(oyE));   sab[0] = fma2(pk(-__low2float(oxE), -__low2float(oyE)), o, sab[0]);
-                    n = pk(__low2float(jxO), __low2float(jyO));   sab[1] = fma2(n, n, sab[1]);
-                    o = pk(__low2float(oxO), __low2float(oyO));   sab[1] = fma2(pk(-__low2float(oxO), -__low2float(oyO)), o, sab[1]);
-                    n = pk(__high2float(jxE), __high2float(jyE)); sab[2] = fma2(n, n, sab[2]);
-                    o = pk(__high2float(oxE), __high2float(oyE)); sab[2] = fma2(pk(-__high2float(oxE), -__high2float(oyE)), o, sab[2]);
-                    n = pk(__high2float(jxO), __high2float(jyO)); sab[3] = fma2(n, n, sab[3]);
-                    o = pk(__high2float(oxO), __high2float(oyO)); sab[3] = fma2(pk(-__high2float(oxO), -__high2float(oyO)), o, sab[3]);
+                    // pixel k of this lane: 0 = E.lo, 1 = O.lo, 2 = E.hi, 3 = O.hi
+                    sa[0] = fhfnma_lo(oxE, fhfma_lo(jxE, sa[0])); sb[0] = fhfnma_lo(oyE, fhfma_lo(jyE, sb[0]));
+                    sa[1] = fhfnma_lo(oxO, fhfma_lo(jxO, sa[1])); sb[1] = fhfnma_lo(oyO, fhfma_lo(jyO, sb[1]));
+                    sa[2] = fhfnma_hi(oxE, fhfma_hi(jxE, sa[2])); sb[2] = fhfnma_hi(oyE, fhfma_hi(jyE, sb[2]));
+                    sa[3] = fhfnma_hi(oxO, fhfma_hi(jxO, sa[3])); sb[3] = fhfnma_hi(oyO, fhfma_hi(jyO, sb[3]));
                 }
-                if (t0 < 12) continue;
+                if (!STEADY && t0 < 12) continue;
 
                 // ---- 4. response row o = r-6 in [ys, ye) -------------------------------------------------------
                 const int orow = r0 + t0 + j - 6;
-                float out0 = 0.f, out1 = 0.f, out2 = 0.f, out3 = 0.f;
-                if (orow >= 2 && orow <= H - 3) {  // warp-uniform; other rows stay zero (R_array zero-initialised)
+                float out[4] = {0.f, 0.f, 0.f, 0.f};
+                if (STEADY || (orow >= 2 && orow <= H - 3)) {  // warp-uniform; other rows stay zero (R_array zero-initialised)
                     // horizontal 5-sums of the running sums (a and b together): columns x-2 .. x+5 needed
-                    const u64 L2 = shfl_up2(sab[2]), L3 = shfl_up2(sab[3]), R0 = shfl_dn2(sab[0]), R1 = shfl_dn2(sab[1]);
-                    const u64 S0 = add2(add2(add2(L2, L3), add2(sab[0], sab[1])), sab[2]);
-                    const u64 S1 = add2(sub2(S0, L2), sab[3]);
+                    const u64 s0 = pk(sa[0], sb[0]), s1 = pk(sa[1], sb[1]), s2 = pk(sa[2], sb[2]), s3 = pk(sa[3], sb[3]);
+                    const u64 L2 = shfl_up2(s2), L3 = shfl_up2(s3), R0 = shfl_dn2(s0), R1 = shfl_dn2(s1);
+                    const u64 S0 = add2(add2(add2(L2, L3), add2(s0, s1)), s2);
+                    const u64 S1 = add2(sub2(S0, L2), s3);
                     const u64 S2 = add2(sub2(S1, L3), R0);
-                    const u64 S3 = add2(sub2(S2, sab[0]), R1);
-                    float A0, B0, A1, B1, A2, B2, A3, B3;
-                    upk(S0, A0, B0); upk(S1, A1, B1); upk(S2, A2, B2); upk(S3, A3, B3);
+                    const u64 S3 = add2(sub2(S2, s0), R1);
+                    float A[4], B[4];
+                    upk(S0, A[0], B[0]); upk(S1, A[1], B[1]); upk(S2, A[2], B[2]); upk(S3, A[3], B[3]);
                     // lambda_min <= min(a, b): rows without a corner-like pixel skip the eigenvalue
-                    const float m = fmaxf(fmaxf(fminf(A0, B0), fminf(A1, B1)), fmaxf(fminf(A2, B2), fminf(A3, B3)));
+                    const float m = fmaxf(fmaxf(fminf(A[0], B[0]), fminf(A[1], B[1])), fmaxf(fminf(A[2], B[2]), fminf(A[3], B[3])));
                     if (__any_sync(FULL, m > thr_need)) {
                         // sum_5x5 Jxy, telescoped: E = B[o-3]+B[o-2]-B[o+2]-B[o+3] per column (steps t-6, t-5, t-1, t)
                         const __half2 eE = __hsub2(__hadd2(bE[j], bE[1 + j]), __hadd2(bE[5 + j], bE[6 + j]));
@@ -367,20 +397,27 @@ k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows, float thr
                         const __half2 e2e4 = prmt_h2(eE, ReE, 0x5432), e3e5 = prmt_h2(eO, ReO, 0x5432);
                         const __half2 cE = __hsub2(__hadd2(LeO, em2e0), __hadd2(e2e4, e3e5));   // (c0, c2)
                         const __half2 cO = __hsub2(__hadd2(em2e0, em1e1), __hadd2(e3e5, ReE));  // (c1, c3)
-                        shi_tomasi2(A0, B0, __low2float(cE), A1, B1, __low2float(cO), thr, out0, out1);
-                        shi_tomasi2(A2, B2, __high2float(cE), A3, B3, __high2float(cO), thr, out2, out3);
+                        shi_tomasi4(A, B, cE, cO, thr, out);
                         if (edge_strip) {
-                            out0 = okc0 ? out0 : 0.f; out1 = okc1 ? out1 : 0.f; out2 = okc2 ? out2 : 0.f; out3 = okc3 ? out3 : 0.f;
+                            out[0] = okc0 ? out[0] : 0.f; out[1] = okc1 ? out[1] : 0.f; out[2] = okc2 ? out[2] : 0.f; out[3] = okc3 ? out[3] : 0.f;
                         }
                     }
                 }
-                if (store_lane && orow < ye) *reinterpret_cast<float4*>(R_p + j * R_pitch) = make_float4(out0, out1, out2, out3);
+                if (store_lane && (STEADY || orow < ye)) *reinterpret_cast<float4*>(R_p + j * R_pitch) = make_float4(out[0], out[1], out[2], out[3]);
             }
         }
         // the ring bases swap: slot (c & 7) ^ 4 of this trip is slot c & 7 of the next
         { const char* t = qa; qa = qb; qb = t; t = ja; ja = jb; jb = t; }
         if (!FROM_BLURRED) blur_p += RB * blur_pitch;
         R_p += RB * R_pitch;
+    };
+    // steady: t0 >= 16 (response rows >= ys+4 >= 2, all rings filled) and blurred row ys+t0-6 <= ye-1 (which puts
+    // the gradient row ys+t0-7 <= H-2, the response row ys+t0-9 <= min(ye-1, H-3), and leaves a further trip)
+    const int t_steady_end = (ye - ys) + 6;
+#pragma unroll 1
+    for (int t0 = 0; t0 < T; t0 += RB) {
+        if (t0 >= 16 && t0 < t_steady_end) trip(std::true_type{}, t0);
+        else trip(std::false_type{}, t0);
     }
 }
 
