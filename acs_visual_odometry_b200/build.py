@@ -17,7 +17,7 @@ LIB = PKG / "libvofront.so"
 SOURCES = ["api.cu", "stencil.cu", "nms_select.cu", "freak.cu", "match.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-         "-Xcompiler", "-fPIC", "-Xptxas", "-v", "--resource-usage"]
+         "-Xcompiler", "-fPIC", "-Xptxas", "-v", "--resource-usage"] + os.environ.get("VO_NVCC_EXTRA", "").split()
 
 
 def _newest_header():

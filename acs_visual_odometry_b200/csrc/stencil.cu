@@ -25,9 +25,10 @@
 //     (Jxy is a difference of differences; BORDER_REFLECT_101 makes it vanish on the image border
 //     exactly as the reference's zero-initialised border does);
 //   * the sums of squares are running sums over the 5-row window in fp32, exact (integers < 2^23);
-//   * the eigenvalue runs only when some pixel of the warp row can pass the threshold:
-//     lambda_min <= min(a, b), so min(a, b) <= threshold - slack decides R = 0 without computing it
-//     (slack covers the fp32 rounding of the reference's formula, see need_margin());
+//   * the eigenvalue is computed for every pixel, branch-free: an earlier version skipped warp rows whose
+//     min(a, b) could not reach the threshold, but on textured frames nearly every row of 116 pixels holds
+//     a corner-like pixel and the branch only kept the scheduler from overlapping the eigenvalue's
+//     dependency chain with the next row's blur (measured: 4 % slower with the skip);
 //   * input rows are requested one trip (four rows) ahead; image borders are mirrored with two lane
 //     shuffles and a byte permute instead of gathers (edge strips only).
 // HBM traffic per pixel: 1 B in, 1 B blurred out, 4 B R out.
@@ -45,11 +46,15 @@
 
 namespace {
 
-constexpr int SW = 112;    // output columns per warp strip
-constexpr int HX = 8;      // column halo on each side (6 needed; 8 keeps the 4-pixel groups aligned)
+constexpr int SW = 116;    // output columns per warp strip: the 128-pixel window minus 6 halo columns each side
+constexpr int HX = 8;      // window start relative to strip*SW (6 halo columns needed; 8 keeps the 4-pixel groups aligned,
+                           // so lane 1 stores only its upper two pixels and lane 30 only its lower two)
 constexpr int NWARP = 4;   // warps per CTA (independent tasks)
 constexpr int RB = 4;      // rows per loop trip; must divide the ring length 8
-constexpr int CTAS_PER_SM = 4;
+#ifndef VO_CTAS
+#define VO_CTAS 4
+#endif
+constexpr int CTAS_PER_SM = VO_CTAS;
 constexpr unsigned FULL = 0xFFFFFFFFu;
 typedef unsigned long long u64;
 
@@ -163,7 +168,7 @@ __device__ __forceinline__ void sts4(const char* p, uint4 v) { *reinterpret_cast
 // images too small for the mirror scheme.  ALIGNED: rows start on 4-byte boundaries (one load per row).
 template <bool FROM_BLURRED, bool GATHER, bool ALIGNED>
 __global__ void __launch_bounds__(32 * NWARP, CTAS_PER_SM)
-k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows, float thr_need) {
+k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows) {
     __shared__ __align__(16) char s_rings[NWARP][RING_BYTES];
     const int lane = threadIdx.x & 31;
     const int task = blockIdx.x * NWARP + (threadIdx.x >> 5);
@@ -175,7 +180,10 @@ k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows, float thr
     const int ys = seg * seg_rows, ye = min(H, ys + seg_rows);
     const int xs = strip * SW - HX;
     const int x = xs + 4 * lane;  // this lane's columns: x .. x+3
-    const bool store_lane = lane >= HX / 4 && lane < 32 - HX / 4 && x < W;
+    // outputs of this strip: columns xs+6 .. xs+121, i.e. lanes 2..29 whole, lane 1 pixels 2-3, lane 30 pixels 0-1
+    const bool store_lane = lane >= 2 && lane < 30 && x < W;
+    const bool store_hi2 = lane == 1 && x + 2 >= 0 && x + 2 < W;
+    const bool store_lo2 = lane == 30 && x < W;
     const uint8_t* __restrict__ in = a.in + (size_t)f * a.in_fstride;
     uint8_t* __restrict__ blur_out = FROM_BLURRED ? nullptr : a.blur + (size_t)f * a.blur_fstride;
     float* __restrict__ R = a.R + (size_t)f * a.R_fstride;
@@ -184,7 +192,7 @@ k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows, float thr
     // gradients are zero outside 1 <= j <= W-2 (cv::Mat::zeros border); packing: E = (px0, px2), O = (px1, px3)
     const __half2 mE = __floats2half2_rn((x >= 1 && x <= W - 2) ? 1.f : 0.f, (x + 2 >= 1 && x + 2 <= W - 2) ? 1.f : 0.f);
     const __half2 mO = __floats2half2_rn((x + 1 >= 1 && x + 1 <= W - 2) ? 1.f : 0.f, (x + 3 >= 1 && x + 3 <= W - 2) ? 1.f : 0.f);
-    const bool edge_strip = (xs < 1) || (xs + SW + 2 * HX > W - 2);  // warp-uniform
+    const bool edge_strip = (xs < 1) || (xs + 128 > W - 2);  // warp-uniform: the 128-pixel window touches a border
     // response columns < 2 and > W-3 stay zero
     const bool okc0 = x >= 2 && x <= W - 3, okc1 = x + 1 >= 2 && x + 1 <= W - 3, okc2 = x + 2 >= 2 && x + 2 <= W - 3,
                okc3 = x + 3 >= 2 && x + 3 <= W - 3;
@@ -323,8 +331,12 @@ k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows, float thr
                 S3 = __dp2a_lo(RE_, 56u | (8u << 8), S3);  S3 = __dp2a_lo(RO_, 28u, S3);
                 const uint32_t hE = __byte_perm(S0, S2, 0x7632), hO = __byte_perm(S1, S3, 0x7632);  // fp16 1024 + B
                 const int rb = r0 + t0 + j - 3;
-                if (store_lane && (STEADY || (rb >= ys && rb < ye)))
-                    *reinterpret_cast<uint32_t*>(blur_p + j * blur_pitch) = __byte_perm(hE, hO, 0x6240);
+                if (STEADY || (rb >= ys && rb < ye)) {
+                    const uint32_t b4 = __byte_perm(hE, hO, 0x6240);
+                    if (store_lane) *reinterpret_cast<uint32_t*>(blur_p + j * blur_pitch) = b4;
+                    if (store_lo2) *reinterpret_cast<uint16_t*>(blur_p + j * blur_pitch) = static_cast<uint16_t>(b4);
+                    if (store_hi2) *reinterpret_cast<uint16_t*>(blur_p + j * blur_pitch + 2) = static_cast<uint16_t>(b4 >> 16);
+                }
                 bE[6 + j] = __hsub2(u2h(hE), k1024);
                 bO[6 + j] = __hsub2(u2h(hO), k1024);
                 sts2(slot_of(qa, qb, j, 256) + 2048, make_uint2(h2u(bE[6 + j]), h2u(bO[6 + j])));
@@ -385,9 +397,7 @@ k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows, float thr
                     const u64 S3 = add2(sub2(S2, s0), R1);
                     float A[4], B[4];
                     upk(S0, A[0], B[0]); upk(S1, A[1], B[1]); upk(S2, A[2], B[2]); upk(S3, A[3], B[3]);
-                    // lambda_min <= min(a, b): rows without a corner-like pixel skip the eigenvalue
-                    const float m = fmaxf(fmaxf(fminf(A[0], B[0]), fminf(A[1], B[1])), fmaxf(fminf(A[2], B[2]), fminf(A[3], B[3])));
-                    if (__any_sync(FULL, m > thr_need)) {
+                    {
                         // sum_5x5 Jxy, telescoped: E = B[o-3]+B[o-2]-B[o+2]-B[o+3] per column (steps t-6, t-5, t-1, t)
                         const __half2 eE = __hsub2(__hadd2(bE[j], bE[1 + j]), __hadd2(bE[5 + j], bE[6 + j]));
                         const __half2 eO = __hsub2(__hadd2(bO[j], bO[1 + j]), __hadd2(bO[5 + j], bO[6 + j]));
@@ -403,7 +413,12 @@ k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows, float thr
                         }
                     }
                 }
-                if (store_lane && (STEADY || orow < ye)) *reinterpret_cast<float4*>(R_p + j * R_pitch) = make_float4(out[0], out[1], out[2], out[3]);
+                if (STEADY || orow < ye) {
+                    float* const q = R_p + j * R_pitch;
+                    if (store_lane) *reinterpret_cast<float4*>(q) = make_float4(out[0], out[1], out[2], out[3]);
+                    if (store_lo2) *reinterpret_cast<float2*>(q) = make_float2(out[0], out[1]);
+                    if (store_hi2) *reinterpret_cast<float2*>(q + 2) = make_float2(out[2], out[3]);
+                }
             }
         }
         // the ring bases swap: slot (c & 7) ^ 4 of this trip is slot c & 7 of the next
@@ -434,12 +449,6 @@ __global__ void k_bgr2gray(const uint8_t* __restrict__ bgr, size_t bgr_pitch, ui
     gray[(size_t)y * gray_pitch + x] = (uint8_t)min(max(iv, 0), 255);
 }
 
-// R_computed <= min(a, b) + need_margin(thr) for every integer a, b in [0, 2^23), integer c: in exact
-// arithmetic R = tr/2 - sqrt((a-b)^2 + 4c^2)/2 <= min(a, b); the fp32 evaluation adds at most
-// ~130 (strongly anisotropic windows: relative error 6*2^-24 of tr <= 2^24) or ~6e-4*min(a, b)
-// (nearly isotropic windows, where tr < 16/7 min(a, b)).  tests/test_oracle.py samples the bound.
-float need_margin(float thr) { return 160.0f + 0.002f * thr; }
-
 int sm_count_cached() {
     static int n = 0;
     if (!n) {
@@ -456,7 +465,7 @@ cudaError_t launch_stencil(const StencilArgs& a, int n_frames, bool from_blurred
     // blurred and R rows are written with 4-byte / 16-byte vector stores at columns that are multiples of 4
     if ((a.R_pitch & 3) || (a.R_fstride & 3) || (!from_blurred && ((a.blur_pitch & 3) || (a.blur_fstride & 3))))
         return cudaErrorInvalidValue;
-    const int n_strips = (a.cols + SW - 1) / SW;
+    const int n_strips = (a.cols + 2 + SW - 1) / SW;  // strip s covers columns [s*SW - 2, s*SW + SW - 2)
     // Segment height: every segment recomputes 12 halo rows, and the grid runs in rounds of
     // (SMs x resident CTAs); pick the split with the smallest rounds x (rows + 12).
     const int slots = sm_count_cached() * CTAS_PER_SM;
@@ -471,10 +480,9 @@ cudaError_t launch_stencil(const StencilArgs& a, int n_frames, bool from_blurred
     const int seg_rows = ((a.rows + best_segs - 1) / best_segs + RB - 1) / RB * RB;
     const int n_segs = (a.rows + seg_rows - 1) / seg_rows;
     const dim3 grid((n_strips * n_segs + NWARP - 1) / NWARP, n_frames);
-    const float tn = a.threshold - need_margin(a.threshold);
     const bool gather = a.cols < 16 || a.rows < 8;
     const bool aligned = ((reinterpret_cast<uintptr_t>(a.in) | a.in_pitch | a.in_fstride) & 3) == 0;
-#define VO_LAUNCH(FB, GA, AL) k_stencil<FB, GA, AL><<<grid, 32 * NWARP, 0, st>>>(a, n_strips, n_segs, seg_rows, tn)
+#define VO_LAUNCH(FB, GA, AL) k_stencil<FB, GA, AL><<<grid, 32 * NWARP, 0, st>>>(a, n_strips, n_segs, seg_rows)
     if (from_blurred) {
         if (gather) VO_LAUNCH(true, true, false);
         else if (aligned) VO_LAUNCH(true, false, true);
