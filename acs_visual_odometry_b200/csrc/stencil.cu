@@ -120,7 +120,7 @@ __device__ __forceinline__ float rsqrt_approx(float x) { float y; asm("rsqrt.app
 // disc + 1e-30 (== disc for disc >= 1): disc == 0 gives exactly 0, and disc < 0 gives NaN, which fails the
 // threshold comparison exactly like the reference's NaN does.
 // Pixel order: A/B index k = pixel k; cE = (c0, c2), cO = (c1, c3) as fp16 (integers <= 2040, exact).
-__device__ __forceinline__ void shi_tomasi4(const float (&A)[4], const float (&B)[4], __half2 cE, __half2 cO, float thr,
+__device__ __forceinline__ void shi_tomasi4(const float (&A)[4], const float (&B)[4], __half2 cE, __half2 cO, const float (&thr)[4],
                                             float (&out)[4]) {
     float cc[4], ab[4], t[4], ntt[4], dz[4];
     cc[0] = fhfma_lo(cE, 0.f); cc[1] = fhfma_lo(cO, 0.f); cc[2] = fhfma_hi(cE, 0.f); cc[3] = fhfma_hi(cO, 0.f);
@@ -143,8 +143,8 @@ __device__ __forceinline__ void shi_tomasi4(const float (&A)[4], const float (&B
         const u64 nsq = fma2(ne, h, ns);
         const u64 r = fma2(nsq, half, mul2(pk(t[q], t[q + 1]), half));
         float r0, r1; upk(r, r0, r1);
-        out[q] = r0 > thr ? r0 : 0.0f;
-        out[q + 1] = r1 > thr ? r1 : 0.0f;
+        out[q] = r0 > thr[q] ? r0 : 0.0f;
+        out[q + 1] = r1 > thr[q + 1] ? r1 : 0.0f;
     }
 }
 
@@ -181,13 +181,13 @@ k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows) {
     const int xs = strip * SW - HX;
     const int x = xs + 4 * lane;  // this lane's columns: x .. x+3
     // outputs of this strip: columns xs+6 .. xs+121, i.e. lanes 2..29 whole, lane 1 pixels 2-3, lane 30 pixels 0-1
-    const bool store_lane = lane >= 2 && lane < 30 && x < W;
-    const bool store_hi2 = lane == 1 && x + 2 >= 0 && x + 2 < W;
-    const bool store_lo2 = lane == 30 && x < W;
+    // lanes 2..29 store their four pixels, lane 1 its upper pair, lane 30 its lower pair
+    const bool st_full = lane >= 2 && lane < 30 && x < W, st_l1 = lane == 1 && x + 2 >= 0 && x + 2 < W, st_l30 = lane == 30 && x < W;
     const uint8_t* __restrict__ in = a.in + (size_t)f * a.in_fstride;
     uint8_t* __restrict__ blur_out = FROM_BLURRED ? nullptr : a.blur + (size_t)f * a.blur_fstride;
     float* __restrict__ R = a.R + (size_t)f * a.R_fstride;
     const float thr = a.threshold;
+    const float kInf = __int_as_float(0x7f800000);
 
     // gradients are zero outside 1 <= j <= W-2 (cv::Mat::zeros border); packing: E = (px0, px2), O = (px1, px3)
     const __half2 mE = __floats2half2_rn((x >= 1 && x <= W - 2) ? 1.f : 0.f, (x + 2 >= 1 && x + 2 <= W - 2) ? 1.f : 0.f);
@@ -196,6 +196,7 @@ k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows) {
     // response columns < 2 and > W-3 stay zero
     const bool okc0 = x >= 2 && x <= W - 3, okc1 = x + 1 >= 2 && x + 1 <= W - 3, okc2 = x + 2 >= 2 && x + 2 <= W - 3,
                okc3 = x + 3 >= 2 && x + 3 <= W - 3;
+    const float thr4[4] = {okc0 ? thr : kInf, okc1 ? thr : kInf, okc2 ? thr : kInf, okc3 ? thr : kInf};  // nothing exceeds +inf
 
     // ---- input access ----------------------------------------------------------------------------------
     // Lanes whose first pixel is inside the row read the aligned word(s) holding x..x+3 (up to 7 bytes past
@@ -226,9 +227,10 @@ k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows) {
     uint32_t pa[RB], pb[RB], psh[RB];  // in-flight input rows
     const int xin = inside ? x : 0;
     const long long in_pitch = (long long)a.in_pitch;
-    auto issue = [&](int row) {  // rows row .. row+3
-        const bool interior = row >= 0 && row + RB <= H;  // warp-uniform: no reflection needed
-        const uint8_t* const p0 = in + (long long)row * in_pitch + xin;
+    const uint8_t* in_next = in + xin;  // this lane's word of the next row to request (valid while that row is interior)
+    auto issue = [&](int row, bool known_interior) {  // rows row .. row+3
+        const bool interior = known_interior || (row >= 0 && row + RB <= H);  // warp-uniform: no reflection needed
+        const uint8_t* const p0 = known_interior ? in_next : in + (long long)row * in_pitch + xin;
 #pragma unroll
         for (int j = 0; j < RB; ++j) {
             const uint8_t* p = p0 + j * in_pitch;
@@ -266,7 +268,8 @@ k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows) {
     const int T = (ye - ys) + 12;
     const int r0 = ys - 6;
     const int load_off = FROM_BLURRED ? -3 : 0;
-    issue(r0 + load_off);
+    issue(r0 + load_off, false);
+    in_next += (long long)(r0 + RB + load_off) * in_pitch;  // trip t0 requests rows r0+t0+RB+load_off ..
     // output row pointers of step t0 (this lane's column), advanced by RB rows per trip
     const long long blur_pitch = (long long)a.blur_pitch, R_pitch = (long long)a.R_pitch;
     uint8_t* blur_p = FROM_BLURRED ? nullptr : blur_out + (long long)(r0 - 3) * blur_pitch + x;
@@ -277,16 +280,19 @@ k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows) {
     // segment run the general form.
     auto trip = [&](auto steady_tag, const int t0) {
         constexpr bool STEADY = decltype(steady_tag)::value;
+        // (a third body specialised for interior strips was tried: 8 % SLOWER, the two steady bodies together no longer
+        // fit the instruction cache; so the edge handling stays predicated on the warp-uniform edge_strip)
+        const bool edge = edge_strip;
         // ---- 0. the four rows requested a trip ago; request the next four -----------------------------------
         uint32_t w[RB];
 #pragma unroll
         for (int j = 0; j < RB; ++j) w[j] = (GATHER || ALIGNED) ? pa[j] : __funnelshift_r(pa[j], pb[j], psh[j]);
-        if (!GATHER && edge_strip) {
+        if (!GATHER && edge) {
 #pragma unroll
             for (int j = 0; j < RB; ++j)
                 w[j] = __byte_perm(__shfl_sync(FULL, w[j], srcA), __shfl_sync(FULL, w[j], srcB), msel);
         }
-        if (STEADY || t0 + RB < T) issue(r0 + t0 + RB + load_off);
+        if (STEADY || t0 + RB < T) issue(r0 + t0 + RB + load_off, STEADY);
 
         // ---- 1. blurred rows r-3 for the four steps ----------------------------------------------------------
         // index i of the local windows = step offset c + 6, c in [-6, 3]
@@ -333,9 +339,11 @@ k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows) {
                 const int rb = r0 + t0 + j - 3;
                 if (STEADY || (rb >= ys && rb < ye)) {
                     const uint32_t b4 = __byte_perm(hE, hO, 0x6240);
-                    if (store_lane) *reinterpret_cast<uint32_t*>(blur_p + j * blur_pitch) = b4;
-                    if (store_lo2) *reinterpret_cast<uint16_t*>(blur_p + j * blur_pitch) = static_cast<uint16_t>(b4);
-                    if (store_hi2) *reinterpret_cast<uint16_t*>(blur_p + j * blur_pitch + 2) = static_cast<uint16_t>(b4 >> 16);
+                    uint8_t* q = blur_p + j * blur_pitch;
+                    asm volatile("" : "+l"(q));  // one address for the three store forms
+                    if (st_full) *reinterpret_cast<uint32_t*>(q) = b4;
+                    if (st_l30) *reinterpret_cast<uint16_t*>(q) = static_cast<uint16_t>(b4);
+                    if (st_l1) *reinterpret_cast<uint16_t*>(q + 2) = static_cast<uint16_t>(b4 >> 16);
                 }
                 bE[6 + j] = __hsub2(u2h(hE), k1024);
                 bO[6 + j] = __hsub2(u2h(hO), k1024);
@@ -369,7 +377,7 @@ k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows) {
                     jxO = __hadd2(__hfma2(dO, two, dE), d2d4);   // (d0,d2) + 2(d1,d3) + (d2,d4)
                     jyE = __hsub2(sm1s1, sO);                    // (s-1,s1) - (s1,s3)
                     jyO = __hsub2(sE, s2s4);                     // (s0,s2) - (s2,s4)
-                    if (edge_strip) { jxE = __hmul2(jxE, mE); jxO = __hmul2(jxO, mO); jyE = __hmul2(jyE, mE); jyO = __hmul2(jyO, mO); }
+                    if (edge) { jxE = __hmul2(jxE, mE); jxO = __hmul2(jxO, mO); jyE = __hmul2(jyE, mE); jyO = __hmul2(jyO, mO); }
                 }
                 // ---- 3. running sums over rows g-4..g: add row g, drop row g-5 ---------------------------------
                 {
@@ -407,17 +415,15 @@ k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows) {
                         const __half2 e2e4 = prmt_h2(eE, ReE, 0x5432), e3e5 = prmt_h2(eO, ReO, 0x5432);
                         const __half2 cE = __hsub2(__hadd2(LeO, em2e0), __hadd2(e2e4, e3e5));   // (c0, c2)
                         const __half2 cO = __hsub2(__hadd2(em2e0, em1e1), __hadd2(e3e5, ReE));  // (c1, c3)
-                        shi_tomasi4(A, B, cE, cO, thr, out);
-                        if (edge_strip) {
-                            out[0] = okc0 ? out[0] : 0.f; out[1] = okc1 ? out[1] : 0.f; out[2] = okc2 ? out[2] : 0.f; out[3] = okc3 ? out[3] : 0.f;
-                        }
+                        shi_tomasi4(A, B, cE, cO, thr4, out);
                     }
                 }
                 if (STEADY || orow < ye) {
-                    float* const q = R_p + j * R_pitch;
-                    if (store_lane) *reinterpret_cast<float4*>(q) = make_float4(out[0], out[1], out[2], out[3]);
-                    if (store_lo2) *reinterpret_cast<float2*>(q) = make_float2(out[0], out[1]);
-                    if (store_hi2) *reinterpret_cast<float2*>(q + 2) = make_float2(out[2], out[3]);
+                    float* q = R_p + j * R_pitch;
+                    asm volatile("" : "+l"(q));
+                    if (st_full) *reinterpret_cast<float4*>(q) = make_float4(out[0], out[1], out[2], out[3]);
+                    if (st_l30) *reinterpret_cast<float2*>(q) = make_float2(out[0], out[1]);
+                    if (st_l1) *reinterpret_cast<float2*>(q + 2) = make_float2(out[2], out[3]);
                 }
             }
         }
@@ -425,14 +431,19 @@ k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows) {
         { const char* t = qa; qa = qb; qb = t; t = ja; ja = jb; jb = t; }
         if (!FROM_BLURRED) blur_p += RB * blur_pitch;
         R_p += RB * R_pitch;
+        in_next += RB * in_pitch;
     };
     // steady: t0 >= 16 (response rows >= ys+4 >= 2, all rings filled) and blurred row ys+t0-6 <= ye-1 (which puts
     // the gradient row ys+t0-7 <= H-2, the response row ys+t0-9 <= min(ye-1, H-3), and leaves a further trip)
-    const int t_steady_end = (ye - ys) + 6;
+    // and the rows it requests for the next trip, up to ys+t0+1+load_off, are image rows (no reflection).
+    const int t_steady_end = min((ye - ys) + 6, H - ys - 1 - load_off);
 #pragma unroll 1
     for (int t0 = 0; t0 < T; t0 += RB) {
-        if (t0 >= 16 && t0 < t_steady_end) trip(std::true_type{}, t0);
-        else trip(std::false_type{}, t0);
+        if (t0 >= 16 && t0 < t_steady_end) {
+            trip(std::true_type{}, t0);
+        } else {
+            trip(std::false_type{}, t0);
+        }
     }
 }
 

@@ -153,7 +153,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--frames", type=int, default=1000)
-    ap.add_argument("--batch", type=int, default=64)
+    ap.add_argument("--batch", type=int, default=100)
     ap.add_argument("--preset", default="vo_gpu_ref", choices=["vo_gpu_ref", "cpu_ref"])
     ap.add_argument("--match-bits", type=int, default=32, choices=[32, 512])
     ap.add_argument("--rects", type=int, default=None)
