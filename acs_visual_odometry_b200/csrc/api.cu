@@ -220,7 +220,11 @@ int vo_create(vo_ctx** out, int device, int max_rows, int max_cols, int max_keyp
     c->img_fstride = c->img_pitch * (size_t)max_rows;
     c->r_pitch = round_up((size_t)max_cols, 4);
     c->r_fstride = c->r_pitch * (size_t)max_rows;
+    // NMS survivors per frame: at least 8 candidates per kept keypoint, and one per 32 pixels for large frames with a
+    // small top-N (a 4K frame of the synthetic generator has ~60 k survivors); overflow is reported, never silent
     c->cand_cap = VO_CAND_CAP_MIN > 8 * max_keypoints ? VO_CAND_CAP_MIN : 8 * max_keypoints;
+    const long long by_area = (long long)max_rows * max_cols / 32;
+    if (by_area > c->cand_cap) c->cand_cap = (int)by_area;
     c->sort_cap = 1;
     while (c->sort_cap < max_keypoints) c->sort_cap <<= 1;
     const size_t ts = (size_t)c->total_slots;

@@ -254,8 +254,15 @@ def main():
     achieved = st_bytes / (st_ms / 1000.0) / 1e9 if st_ms > 0 else 0.0
     kernel_ms = {k: round(v[0] / max(1, min(args.steps, 3)), 4) for k, v in prof.items()}
     tot_ms = sum(kernel_ms.values()) or 1.0
+    traffic, traffic_src = None, None   # DRAM bytes per launch from the committed ncu --set full capture of this batch size
+    tp = ROOT / "profiles" / "stencil_traffic.json"
+    if tp.exists():
+        tj = json.loads(tp.read_text())
+        if (tj.get("batch"), tj.get("rows"), tj.get("cols")) == (min(args.batch, n), ROWS, COLS):
+            traffic, traffic_src = tj["dram_bytes_per_launch"], tj["source"]
     roofline = {"kernel": "k_stencil (blur+gradients+structure tensor+Shi-Tomasi response)", "bound": "hbm", "achieved": achieved,
-                "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
+                "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": STENCIL_BYTES_PER_PX * px_per_launch,
                 "avg_launch_ms": st_ms / max(st_n, 1), "share_of_step": kernel_ms["stencil"] / tot_ms}
 
