@@ -270,7 +270,7 @@ def main():
         "metric": "frames/s (detect+FREAK+match)", "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
         "warmup": W, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u8/i32/fp32", "data": "synthetic", "config": workload_config(args, n),
-        "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms,
+        "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": world * h2d, "d2h_bytes_per_step": world * d2h, "ms_per_step": e2e_ms,
                 "timing": "wall clock around the synchronous C-ABI call vo_sequence_run, max over ranks"},
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "kernel_ms_per_step": kernel_ms,
         "keypoints_per_frame": float(np.mean(nk)), "matches_per_pair": float(np.mean(nm)) if len(nm) else 0.0,
