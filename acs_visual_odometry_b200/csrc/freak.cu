@@ -36,7 +36,9 @@ constexpr int FK_GROUP = 6;  // pairs per inner-loop trip
 constexpr int FK_TABLE = 1008;  // sum over p of 6*ceil((42-p)/6)
 
 struct __align__(16) PairW { float whx, why, wlx, wly; };
-__constant__ PairW c_w[FK_TABLE];
+constexpr int FK_GROUPS = FK_TABLE / FK_GROUP;  // 168 groups of six pairs, in the reference's pair order
+__constant__ PairW c_w[FK_TABLE + FK_GROUP];    // + one dummy group so that the look-ahead loads stay in bounds
+__constant__ short2 c_grp[FK_GROUPS + 1];       // group -> (first point p, first second point r)
 __constant__ signed char c_px[VO_FREAK_POINTS];
 __constant__ signed char c_py[VO_FREAK_POINTS];
 
@@ -67,25 +69,34 @@ __global__ void __launch_bounds__(FK_NT) k_freak(const FreakArgs a) {
     // O += RN(ic * d / |d|) over the 903 pairs in the reference's order; (x, y) components packed.
     // The product of the packed multiply feeds only the addend of the FMA, and the FMA only the addend of
     // the sum, so ptxas has nothing to contract.
+    // The loop runs over the 168 groups of six pairs, two per trip with ping-pong register sets: the weights
+    // (constant bank, uniform datapath) and samples (shared memory) of the next group are requested before the
+    // running group is evaluated, so their latency hides behind its 30 instructions; without the look-ahead every
+    // group stalled on its own constant loads (ncu: 43 % of the loop's samples on the short scoreboard).
     u64 o2 = 0ull;
-    int k = 0;
-#pragma unroll 1
-    for (int p = 0; p < VO_FREAK_POINTS - 1; ++p) {
-        const float vp = s_v[p][t];
-        const int groups = (VO_FREAK_POINTS - 1 - p + FK_GROUP - 1) / FK_GROUP;
-        const float* sv = &s_v[VO_FREAK_POINTS - FK_GROUP * groups][t];
-#pragma unroll 1
-        for (int g = 0; g < groups; ++g) {
+    PairW wa[FK_GROUP], wb[FK_GROUP];
+    float va[FK_GROUP], vb[FK_GROUP], vpa, vpb;
+    auto load = [&](PairW (&w)[FK_GROUP], float (&v)[FK_GROUP], float& vp, int G) {
+        const short2 g = c_grp[G];  // uniform
+        vp = s_v[g.x][t];
 #pragma unroll
-            for (int i = 0; i < FK_GROUP; ++i) {
-                const PairW w = c_w[k + i];  // uniform index: constant-bank load on the uniform datapath
-                const float ic = __fsub_rn(vp, sv[i * FK_NT]);
-                const u64 ic2 = pk(ic, ic);
-                o2 = add2(o2, fma2(ic2, pk(w.whx, w.why), mul2(ic2, pk(w.wlx, w.wly))));
-            }
-            k += FK_GROUP;
-            sv += FK_GROUP * FK_NT;
+        for (int i = 0; i < FK_GROUP; ++i) { w[i] = c_w[G * FK_GROUP + i]; v[i] = s_v[g.y + i][t]; }
+    };
+    auto eval = [&](const PairW (&w)[FK_GROUP], const float (&v)[FK_GROUP], float vp) {
+#pragma unroll
+        for (int i = 0; i < FK_GROUP; ++i) {
+            const float ic = __fsub_rn(vp, v[i]);
+            const u64 ic2 = pk(ic, ic);
+            o2 = add2(o2, fma2(ic2, pk(w[i].whx, w[i].why), mul2(ic2, pk(w[i].wlx, w[i].wly))));
         }
+    };
+    load(wa, va, vpa, 0);
+#pragma unroll 1
+    for (int G = 0; G < FK_GROUPS; G += 2) {
+        load(wb, vb, vpb, G + 1);
+        eval(wa, va, vpa);
+        load(wa, va, vpa, G + 2);  // G + 2 == FK_GROUPS on the last trip: the dummy group
+        eval(wb, vb, vpb);
     }
     float ox, oy;
     upk(o2, ox, oy);
@@ -147,7 +158,7 @@ __global__ void k_unpack(const uint32_t* __restrict__ packed, int n, uint8_t* __
 }  // namespace
 
 cudaError_t freak_upload_tables() {
-    static PairW tab[FK_TABLE];
+    static PairW tab[FK_TABLE + FK_GROUP];  // the dummy group stays zero
     int k = 0;
     for (int p = 0; p < VO_FREAK_POINTS - 1; ++p) {
         const int groups = (VO_FREAK_POINTS - 1 - p + FK_GROUP - 1) / FK_GROUP;
@@ -165,7 +176,16 @@ cudaError_t freak_upload_tables() {
         }
     }
     if (k != FK_TABLE) return cudaErrorInvalidValue;
+    static short2 grp[FK_GROUPS + 1];
+    int gi = 0;
+    for (int p = 0; p < VO_FREAK_POINTS - 1; ++p) {
+        const int groups = (VO_FREAK_POINTS - 1 - p + FK_GROUP - 1) / FK_GROUP;
+        for (int g = 0; g < groups; ++g, ++gi) grp[gi] = make_short2((short)p, (short)(VO_FREAK_POINTS - FK_GROUP * groups + FK_GROUP * g));
+    }
+    if (gi != FK_GROUPS) return cudaErrorInvalidValue;
+    grp[FK_GROUPS] = make_short2(0, 0);
     cudaError_t e;
+    if ((e = cudaMemcpyToSymbol(c_grp, grp, sizeof(grp))) != cudaSuccess) return e;
     if ((e = cudaMemcpyToSymbol(c_w, tab, sizeof(tab))) != cudaSuccess) return e;
     if ((e = cudaMemcpyToSymbol(c_px, VO_FREAK_PX, sizeof(VO_FREAK_PX))) != cudaSuccess) return e;
     if ((e = cudaMemcpyToSymbol(c_py, VO_FREAK_PY, sizeof(VO_FREAK_PY))) != cudaSuccess) return e;

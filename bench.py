@@ -92,6 +92,34 @@ def dist_env():
     return rank, world, local
 
 
+def bind_to_gpu_numa(gpu_index):
+    """Pin this rank (and so its pinned host buffers, first touched by it) to the CPUs of the NUMA node its GPU hangs
+    off: with 8 ranks streaming 50 GB/s each, frames crossing the socket interconnect would cap the end-to-end rate.
+    Returns a short description for the JSON line; any failure leaves the affinity untouched."""
+    try:
+        import pynvml as nv
+        nv.nvmlInit()
+        bus = nv.nvmlDeviceGetPciInfo(nv.nvmlDeviceGetHandleByIndex(gpu_index)).busId
+        bus = (bus.decode() if isinstance(bus, bytes) else bus).lower()
+        nv.nvmlShutdown()
+        if len(bus.split(":")[0]) == 8:  # NVML prints an 8-digit PCI domain, sysfs a 4-digit one
+            bus = bus[4:]
+        node = int(Path(f"/sys/bus/pci/devices/{bus}/numa_node").read_text())
+        if node < 0:
+            return "numa: single node"
+        cpus = set()
+        for part in Path(f"/sys/devices/system/node/node{node}/cpulist").read_text().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return f"numa: node {node} has no allowed cpus"
+        os.sched_setaffinity(0, cpus)
+        return f"numa: node {node}, {len(cpus)} cpus"
+    except Exception as e:
+        return f"numa: unbound ({type(e).__name__})"
+
+
 def reference_arm(args, rank, world):
     """The reference's own CPU implementation (oracle/_ref/libvoref.so = its TUs compiled unmodified), all host
     threads, default BLOCK_SIZE=100; each step a bounded sample of the same workload."""
@@ -178,7 +206,10 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a B200: the front-end has no CPU fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
+    numa = bind_to_gpu_numa(local)
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "").upper() not in ("INFO", "TRACE"):
+            os.environ["NCCL_DEBUG"] = "WARN"  # keep stdout to the one JSON line (NCCL_DEBUG=VERSION prints a banner there)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     W = max(args.warmup, 3)
 
@@ -272,7 +303,7 @@ def main():
         "dtype": "u8/i32/fp32", "data": "synthetic", "config": workload_config(args, n),
         "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": world * h2d, "d2h_bytes_per_step": world * d2h, "ms_per_step": e2e_ms,
                 "timing": "wall clock around the synchronous C-ABI call vo_sequence_run, max over ranks"},
-        "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "kernel_ms_per_step": kernel_ms,
+        "gpu_launches": int(launches), "clocks": clocks, "host_binding": numa, "roofline": roofline, "kernel_ms_per_step": kernel_ms,
         "keypoints_per_frame": float(np.mean(nk)), "matches_per_pair": float(np.mean(nm)) if len(nm) else 0.0,
         "compares_per_s": float(world * np.sum(nk[:-1].astype(np.float64) * nk[1:]) / (ms_step / 1000.0)),
         "match_mode": "REF32" if args.match_bits == 32 else "FULL512",
