@@ -113,6 +113,22 @@ def test_get_pose_matches_restatement_and_truth():
     assert "Degenerate" in str(e.value)
 
 
+def test_get_pose_against_opencv_golden():
+    """tests/golden/pose_kat.npz: PoseUpdate::getPose mirrored line by line on the reference's own third-party calls
+    (Python cv2 4.13: SVDecomp, undistortPoints, triangulatePoints), generated by tests/golden/make_golden_pose.py.
+    The SVD's sign freedom permutes the four candidates, so the vote LIST is compared as a multiset; the selected
+    (R, t) is unique.  Tolerance 1e-9 (double arithmetic on both sides; measured 1e-15)."""
+    g = np.load(Path(__file__).parent / "golden" / "pose_kat.npz")
+    for k in range(int(g["n_cases"])):
+        F, p1, p2, step = g[f"F{k}"], g[f"p1_{k}"], g[f"p2_{k}"], float(g[f"step{k}"])
+        R, t, votes = host.get_pose(F, p1, p2, gt_step=step)
+        assert np.allclose(R, g[f"R{k}"], atol=1e-9) and np.allclose(t, g[f"t{k}"], atol=1e-9), k
+        assert votes == int(g[f"votes{k}"].max())
+        Ro, to, votes_o = ho.get_pose(F, p1, p2, step)
+        assert np.allclose(Ro, g[f"R{k}"], atol=1e-9) and np.allclose(to, g[f"t{k}"], atol=1e-9), k
+        assert sorted(votes_o) == sorted(g[f"votes{k}"].tolist())
+
+
 def test_formats():
     line = "9.999978e-01 5.272628e-04 -2.066935e-03 -4.690294e-02 -5.296506e-04 9.999992e-01 -1.154865e-03 -2.839928e-02 2.066324e-03 1.155958e-03 9.999971e-01 8.586941e-01"
     T = host.read_gt_line(line)
