@@ -63,6 +63,66 @@ __global__ void __launch_bounds__(MT_NT) k_match(const MatchArgs a) {
     if (qi < n1) a.partial[((size_t)pair * VO_MATCH_SPLITS + split) * a.max_kp + qi] = make_uint2(m1, m2);
 }
 
+// REF32 specialisation.  A compare is XOR + POPC + key + three min/max; the integer ALU (16 lanes per clock and
+// scheduler) would be the limit long before the POPC unit, so the bookkeeping runs two compares per instruction on
+// 16-bit keys: inside a tile of 128 train descriptors the key is dist << 7 | row (dist <= 32: 13 bits), even rows in
+// the low and odd rows in the high half of a register, tracked with VIMNMX.U16x2; the products that build the keys
+// run on the FMA pipe (IMAD).  After each tile the four 16-bit survivors are widened to the global dist << 16 | index
+// keys.  Same (dist, index) order as the 32-bit keys, so the result is identical.
+__device__ __forceinline__ uint32_t min2u(uint32_t a, uint32_t b) { uint32_t d; asm("min.u16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b)); return d; }
+__device__ __forceinline__ uint32_t max2u(uint32_t a, uint32_t b) { uint32_t d; asm("max.u16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b)); return d; }
+__device__ __forceinline__ void push_key2(uint32_t k2, uint32_t& m1, uint32_t& m2) {
+    m2 = min2u(m2, max2u(m1, k2));
+    m1 = min2u(m1, k2);
+}
+__device__ __forceinline__ void widen_key(uint32_t k16, int j0, uint32_t& m1, uint32_t& m2) {
+    const uint32_t d = k16 >> 7;
+    if (d <= 32u) push_key((d << 16) | (uint32_t)(j0 + (int)(k16 & 127u)), m1, m2);  // d > 32: empty slot or padding row
+}
+
+__global__ void __launch_bounds__(MT_NT) k_match_ref32(const MatchArgs a) {
+    __shared__ __align__(16) uint32_t s_t[MT_TILE];
+    const int pair = blockIdx.z, split = blockIdx.y;
+    const int qs = a.qslot[pair], ts = a.tslot[pair];
+    const int n1 = a.nkp[qs], n2 = a.nkp[ts];
+    if ((int)blockIdx.x * MT_NT >= n1) return;
+    const int qi = blockIdx.x * MT_NT + threadIdx.x;
+    const uint32_t* __restrict__ td = a.desc + (size_t)ts * a.kp_stride * 16;
+    const uint32_t q = qi < n1 ? a.desc[((size_t)qs * a.kp_stride + qi) * 16] : 0u;
+
+    const int chunk = (n2 + VO_MATCH_SPLITS - 1) / VO_MATCH_SPLITS;
+    const int j_begin = split * chunk, j_end = min(n2, j_begin + chunk);
+    uint32_t m1 = 0xFFFFFFFFu, m2 = 0xFFFFFFFFu;
+    for (int j0 = j_begin; j0 < j_end; j0 += MT_TILE) {
+        const int cnt = min(MT_TILE, j_end - j0);
+        __syncthreads();
+        if ((int)threadIdx.x < cnt) s_t[threadIdx.x] = td[(size_t)(j0 + threadIdx.x) * 16];
+        __syncthreads();
+        uint32_t t1 = 0xFFFFFFFFu, t2 = 0xFFFFFFFFu;  // per-tile trackers: (even rows | odd rows << 16)
+        uint32_t rc = 0x00010000u;                    // rows (r, r+1) of the running group
+        const int full = cnt & ~3;
+        const uint4* s4 = reinterpret_cast<const uint4*>(s_t);
+#pragma unroll 4
+        for (int r = 0; r < full; r += 4) {
+            const uint4 v = s4[r >> 2];
+            const uint32_t d0 = __popc(q ^ v.x), d1 = __popc(q ^ v.y), d2 = __popc(q ^ v.z), d3 = __popc(q ^ v.w);
+            push_key2(d1 * 0x800000u + (d0 * 128u + rc), t1, t2);
+            push_key2(d3 * 0x800000u + (d2 * 128u + (rc + 0x00020002u)), t1, t2);
+            rc += 0x00040004u;
+        }
+        if (full < cnt) {  // last, partial group: rows beyond cnt get distance 63 and are dropped when widening
+            const uint4 v = s4[full >> 2];
+            const uint32_t d0 = __popc(q ^ v.x);
+            const uint32_t d1 = full + 1 < cnt ? __popc(q ^ v.y) : 63u, d2 = full + 2 < cnt ? __popc(q ^ v.z) : 63u;
+            push_key2(d1 * 0x800000u + (d0 * 128u + rc), t1, t2);
+            push_key2(63u * 0x800000u + (d2 * 128u + (rc + 0x00020002u)), t1, t2);
+        }
+        widen_key(t1 & 0xFFFFu, j0, m1, m2); widen_key(t1 >> 16, j0, m1, m2);
+        widen_key(t2 & 0xFFFFu, j0, m1, m2); widen_key(t2 >> 16, j0, m1, m2);
+    }
+    if (qi < n1) a.partial[((size_t)pair * VO_MATCH_SPLITS + split) * a.max_kp + qi] = make_uint2(m1, m2);
+}
+
 constexpr int FN_NT = 1024;
 
 __global__ void __launch_bounds__(FN_NT) k_finalize(const MatchArgs a) {
@@ -118,7 +178,7 @@ __global__ void __launch_bounds__(FN_NT) k_finalize(const MatchArgs a) {
 cudaError_t launch_match(const MatchArgs& a, int n_pairs, int max_n1, cudaStream_t st) {
     if (n_pairs <= 0 || max_n1 <= 0) return cudaSuccess;
     const dim3 grid((max_n1 + MT_NT - 1) / MT_NT, VO_MATCH_SPLITS, n_pairs);
-    if (a.match_bits == VO_MATCH_REF32) k_match<1><<<grid, MT_NT, 0, st>>>(a);
+    if (a.match_bits == VO_MATCH_REF32) k_match_ref32<<<grid, MT_NT, 0, st>>>(a);
     else k_match<16><<<grid, MT_NT, 0, st>>>(a);
     return cudaGetLastError();
 }
