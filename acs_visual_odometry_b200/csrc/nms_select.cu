@@ -15,7 +15,7 @@
 
 namespace {
 
-constexpr int NMS_ROWS = 4;                       // rows per warp (all loads issued before the first test)
+constexpr int NMS_ROWS = 4;                       // rows per warp (all loads issued before the first test); 2, 6, 8 measured slower
 constexpr int NMS_TILE_PX = 8 * NMS_ROWS * 128;   // pixels per CTA: 8 warps x NMS_ROWS rows x 128 columns
 constexpr int NMS_STAGE = NMS_TILE_PX / 4;        // strict maxima are never 8-adjacent: at most one per 2x2 cell
 

@@ -168,13 +168,15 @@ __device__ __forceinline__ void sts4(const char* p, uint4 v) { *reinterpret_cast
 // images too small for the mirror scheme.  ALIGNED: rows start on 4-byte boundaries (one load per row).
 template <bool FROM_BLURRED, bool GATHER, bool ALIGNED>
 __global__ void __launch_bounds__(32 * NWARP, CTAS_PER_SM)
-k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows) {
+k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows, int n_tasks) {
     __shared__ __align__(16) char s_rings[NWARP][RING_BYTES];
     const int lane = threadIdx.x & 31;
-    const int task = blockIdx.x * NWARP + (threadIdx.x >> 5);
-    if (task >= n_strips * n_segs) return;  // whole warp
+    // tasks = (frame, row segment, strip), numbered across the whole batch so that no warp slot of a CTA idles
+    const int gtask = blockIdx.x * NWARP + (threadIdx.x >> 5);
+    if (gtask >= n_tasks) return;  // whole warp
     char* const ring = s_rings[threadIdx.x >> 5];
-    const int f = blockIdx.y;
+    const int per_frame = n_strips * n_segs;
+    const int f = gtask / per_frame, task = gtask - f * per_frame;
     const int strip = task % n_strips, seg = task / n_strips;
     const int H = a.rows, W = a.cols;
     const int ys = seg * seg_rows, ye = min(H, ys + seg_rows);
@@ -484,16 +486,18 @@ cudaError_t launch_stencil(const StencilArgs& a, int n_frames, bool from_blurred
     long long best_cost = -1;
     for (int n_segs = 1; n_segs <= (a.rows + 15) / 16; ++n_segs) {
         const int sr = ((a.rows + n_segs - 1) / n_segs + RB - 1) / RB * RB;
-        const long long ctas = (long long)((n_strips * n_segs + NWARP - 1) / NWARP) * n_frames;
+        const long long ctas = ((long long)n_strips * n_segs * n_frames + NWARP - 1) / NWARP;
         const long long cost = ((ctas + slots - 1) / slots) * (sr + 12);
         if (best_cost < 0 || cost < best_cost) { best_cost = cost; best_segs = n_segs; }
     }
     const int seg_rows = ((a.rows + best_segs - 1) / best_segs + RB - 1) / RB * RB;
     const int n_segs = (a.rows + seg_rows - 1) / seg_rows;
-    const dim3 grid((n_strips * n_segs + NWARP - 1) / NWARP, n_frames);
+    const long long n_tasks = (long long)n_strips * n_segs * n_frames;
+    if (n_tasks > 0x7FFFFFFFll) return cudaErrorInvalidValue;
+    const dim3 grid((unsigned)((n_tasks + NWARP - 1) / NWARP));
     const bool gather = a.cols < 16 || a.rows < 8;
     const bool aligned = ((reinterpret_cast<uintptr_t>(a.in) | a.in_pitch | a.in_fstride) & 3) == 0;
-#define VO_LAUNCH(FB, GA, AL) k_stencil<FB, GA, AL><<<grid, 32 * NWARP, 0, st>>>(a, n_strips, n_segs, seg_rows)
+#define VO_LAUNCH(FB, GA, AL) k_stencil<FB, GA, AL><<<grid, 32 * NWARP, 0, st>>>(a, n_strips, n_segs, seg_rows, (int)n_tasks)
     if (from_blurred) {
         if (gather) VO_LAUNCH(true, true, false);
         else if (aligned) VO_LAUNCH(true, false, true);

@@ -181,7 +181,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--frames", type=int, default=1000)
-    ap.add_argument("--batch", type=int, default=100)
+    ap.add_argument("--batch", type=int, default=200, help="frames per launch of the resident path (200 x 11 strips = 2200 warps: one wave)")
+    ap.add_argument("--e2e-batch", type=int, default=100, help="frames per pipelined chunk of vo_sequence_run (copy-bound: small chunks shorten the pipeline's head and tail)")
     ap.add_argument("--preset", default="vo_gpu_ref", choices=["vo_gpu_ref", "cpu_ref"])
     ap.add_argument("--match-bits", type=int, default=32, choices=[32, 512])
     ap.add_argument("--rects", type=int, default=None)
@@ -216,7 +217,7 @@ def main():
     params = Params.vo_gpu_ref() if args.preset == "vo_gpu_ref" else Params.cpu_ref()
     params.match_bits = args.match_bits
     n = args.frames
-    vo = VoFront(ROWS, COLS, params.max_keypoints, 2 * args.batch, device=local)
+    vo = VoFront(ROWS, COLS, params.max_keypoints, 2 * max(args.batch, args.e2e_batch), device=local)
     pinned = PinnedBuffer((n, ROWS, COLS), np.uint8)
     frames = make_sequence(n, ROWS, COLS, seed=args.seed + 1000 * rank, n_rects=args.rects, out=pinned.array)
 
@@ -257,11 +258,11 @@ def main():
            PinnedBuffer((max(n - 1, 1), mk, 2), np.int32))
     out_arrays = tuple(b.array for b in out)
     for _ in range(W):
-        vo.sequence_run(frames, params, args.batch, out=out_arrays)
+        vo.sequence_run(frames, params, args.e2e_batch, out=out_arrays)
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        vo.sequence_run(frames, params, args.batch, out=out_arrays)   # synchronous: returns when results are on the host
+        vo.sequence_run(frames, params, args.e2e_batch, out=out_arrays)   # synchronous: returns when results are on the host
     e2e_ms = max_over_ranks(1000.0 * (time.perf_counter() - t0) / args.steps)
     barrier()
     clocks = sampler.stop()   # sampled from the first warm-up pass to the end of the end-to-end passes
@@ -301,7 +302,7 @@ def main():
         "metric": "frames/s (detect+FREAK+match)", "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
         "warmup": W, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u8/i32/fp32", "data": "synthetic", "config": workload_config(args, n),
-        "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": world * h2d, "d2h_bytes_per_step": world * d2h, "ms_per_step": e2e_ms,
+        "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": world * h2d, "d2h_bytes_per_step": world * d2h, "ms_per_step": e2e_ms, "batch": args.e2e_batch,
                 "timing": "wall clock around the synchronous C-ABI call vo_sequence_run, max over ranks"},
         "gpu_launches": int(launches), "clocks": clocks, "host_binding": numa, "roofline": roofline, "kernel_ms_per_step": kernel_ms,
         "keypoints_per_frame": float(np.mean(nk)), "matches_per_pair": float(np.mean(nm)) if len(nm) else 0.0,
