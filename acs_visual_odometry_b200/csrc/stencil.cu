@@ -40,6 +40,7 @@
 // result (exact products by 0.5 / 4, sums, the sqrt refinement's intended FMAs).
 #include <cuda_fp16.h>
 
+#include <cstdlib>
 #include <type_traits>
 
 #include "vo_internal.cuh"
@@ -485,17 +486,15 @@ cudaError_t launch_stencil(const StencilArgs& a, int n_frames, bool from_blurred
     if ((a.R_pitch & 3) || (a.R_fstride & 3) || (!from_blurred && ((a.blur_pitch & 3) || (a.blur_fstride & 3))))
         return cudaErrorInvalidValue;
     const int n_strips = (a.cols + 2 + SW - 1) / SW;  // strip s covers columns [s*SW - 2, s*SW + SW - 2)
-    // Segment height: every segment recomputes 12 halo rows, and the grid runs in rounds of
-    // (SMs x resident CTAs); pick the split with the smallest rounds x (rows + 12).
-    const int slots = sm_count_cached() * CTAS_PER_SM;
-    int best_segs = 1;
-    long long best_cost = -1;
-    for (int n_segs = 1; n_segs <= (a.rows + 15) / 16; ++n_segs) {
-        const int sr = ((a.rows + n_segs - 1) / n_segs + RB - 1) / RB * RB;
-        const long long ctas = ((long long)n_strips * n_segs * n_frames + NWARP - 1) / NWARP;
-        const long long cost = ((ctas + slots - 1) / slots) * (sr + 12);
-        if (best_cost < 0 || cost < best_cost) { best_cost = cost; best_segs = n_segs; }
-    }
+    // Segment height.  Every segment recomputes 12 halo rows, but the kernel is latency-bound per warp, so what
+    // matters most is that all resident warp slots stay occupied to the end: a sweep over segment counts (KITTI at
+    // batch 64/100/200, 4K at batch 1/16/64, profiles/README.md) is flat within 5 % around "three tasks per resident
+    // warp slot" and 10-25 % worse for a single under-filled wave.  Segments stay at least 48 rows high.
+    const int slots = sm_count_cached() * CTAS_PER_SM * NWARP;
+    const long long cols_tasks = (long long)n_strips * n_frames;
+    int best_segs = (int)((3LL * slots + cols_tasks / 2) / cols_tasks);
+    best_segs = max(1, min(best_segs, max(1, a.rows / 48)));
+    if (const char* e = getenv("VO_STENCIL_SEGS")) { const int v = atoi(e); if (v >= 1 && v <= (a.rows + 15) / 16) best_segs = v; }  // tuning aid
     const int seg_rows = ((a.rows + best_segs - 1) / best_segs + RB - 1) / RB * RB;
     const int n_segs = (a.rows + seg_rows - 1) / seg_rows;
     const long long n_tasks = (long long)n_strips * n_segs * n_frames;
