@@ -300,6 +300,41 @@ def test_batch_and_sequence_equal_single_frames(vo_small, oracle):
             assert np.array_equal(pr2[k, :nm2[k]], want_pairs[k])
 
 
+def test_large_batches_and_every_segment_count(oracle, monkeypatch):
+    """The resident path at the bench's batch size (250 frames per launch) and the stencil's row-segment split (1..7
+    segments, forced through the VO_STENCIL_SEGS tuning aid) give the results of frame-by-frame extraction; frame 0 is
+    also checked against the CPU oracle."""
+    from acs_visual_odometry_b200 import Params, VoFront
+    from acs_visual_odometry_b200.synth import make_sequence
+    n = 260
+    frames = make_sequence(n, 120, 250, seed=33, n_rects=90)
+    p = Params(25000.0, 3, 300)
+    with VoFront(120, 250, 300, 500) as vo:
+        vo.sequence_upload(frames)
+        vo.sequence_run_resident(p, 250)
+        nk0, kp0, nm0, pr0 = vo.sequence_fetch()
+        assert nk0.min() > 10 and nm0.min() > 3
+        kp_o, _ = oracle.extract(frames[0], p.threshold, p.nms_window, p.max_keypoints)
+        assert np.array_equal(kp0[0, :nk0[0]], kp_o)
+        for k in (0, 1, 128, 249, 250, 259):
+            vo.extract(frames[k], p, slot=0)
+            kp, _, _ = vo.fetch(0)
+            assert np.array_equal(kp0[k, :nk0[k]], kp), k
+
+        def same(nk, kp, nm, pr):  # rows past the counts are unspecified
+            return (np.array_equal(nk, nk0) and np.array_equal(nm, nm0)
+                    and all(np.array_equal(kp[k, :nk[k]], kp0[k, :nk[k]]) for k in range(n))
+                    and all(np.array_equal(pr[k, :nm[k]], pr0[k, :nm[k]]) for k in range(n - 1)))
+
+        for segs in (1, 2, 5, 7):
+            monkeypatch.setenv("VO_STENCIL_SEGS", str(segs))
+            vo.sequence_run_resident(p, 100)
+            nk, kp, nm, pr = vo.sequence_fetch()
+            assert same(nk, kp, nm, pr), segs
+        monkeypatch.delenv("VO_STENCIL_SEGS")
+        assert same(*vo.sequence_run(frames, p, 250))
+
+
 def test_errors_are_loud(vo_small):
     from acs_visual_odometry_b200 import Params, VoError
     img = np.zeros((100, 120), np.uint8)
