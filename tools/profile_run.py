@@ -12,8 +12,8 @@ sys.path.insert(0, str(Path(__file__).resolve().parents[1]))
 from acs_visual_odometry_b200 import Params, VoFront  # noqa: E402
 from acs_visual_odometry_b200.synth import make_sequence  # noqa: E402
 
-frames_n = int(sys.argv[1]) if len(sys.argv) > 1 else 400
-batch = int(sys.argv[2]) if len(sys.argv) > 2 else 200
+frames_n = int(sys.argv[1]) if len(sys.argv) > 1 else 500
+batch = int(sys.argv[2]) if len(sys.argv) > 2 else 250
 bits = int(sys.argv[3]) if len(sys.argv) > 3 else 32
 frames = make_sequence(frames_n, 376, 1241, seed=0)
 p = Params.vo_gpu_ref()

@@ -13,6 +13,6 @@ for b in 1 2 4 8 16 32 64; do
   $K --tag cfg4_4k_batch$b --rows 2160 --cols 3840 --frames 64 --batch $b --passes 2 >> $OUT
 done
 # config 2 for the record, REF32 and FULL512
-$K --tag cfg2_kitti --frames 1000 --batch 200 --bits 32 >> $OUT
-$K --tag cfg2_kitti_full512 --frames 1000 --batch 200 --bits 512 >> $OUT
+$K --tag cfg2_kitti --frames 1000 --batch 250 --bits 32 >> $OUT
+$K --tag cfg2_kitti_full512 --frames 1000 --batch 250 --bits 512 >> $OUT
 cat $OUT | cut -c1-700
