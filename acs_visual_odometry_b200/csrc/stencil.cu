@@ -8,8 +8,8 @@
 //
 // Design (B200).  At 6 B/px the kernel is issue-bound long before it is HBM-bound, so every choice below
 // buys instructions:
-//   * one WARP owns a strip of 128 columns (4 adjacent pixels per lane, 8-column halo each side -> 112
-//     output columns) and marches down the rows of its segment, FOUR rows per loop trip.  No block
+//   * one WARP owns a 128-pixel window (4 adjacent pixels per lane) that yields 116 output columns (6 halo
+//     columns each side) and marches down the rows of its segment, FOUR rows per loop trip.  No block
 //     barrier; horizontal neighbours come from warp shuffles, vertical history (raw rows, blurred rows,
 //     gradient rows) from per-lane rings in shared memory that only their owner reads back;
 //   * the four rows of a trip share their ring reads (10 raw rows feed 4 blurred rows, 10 blurred rows
@@ -24,7 +24,8 @@
 //   * sum_5x5 Jxy telescopes to E[x-3]+E[x-2]-E[x+2]-E[x+3], E[x] = B[o-3][x]+B[o-2][x]-B[o+2][x]-B[o+3][x]
 //     (Jxy is a difference of differences; BORDER_REFLECT_101 makes it vanish on the image border
 //     exactly as the reference's zero-initialised border does);
-//   * the sums of squares are running sums over the 5-row window in fp32, exact (integers < 2^23);
+//   * the sums of squares are running sums over the 5-row window in fp32, exact (integers < 2^23), updated with
+//     Blackwell's mixed-precision FMA (fp16 factors from either register half, fp32 accumulator: SASS FHFMA);
 //   * the eigenvalue is computed for every pixel, branch-free: an earlier version skipped warp rows whose
 //     min(a, b) could not reach the threshold, but on textured frames nearly every row of 116 pixels holds
 //     a corner-like pixel and the branch only kept the scheduler from overlapping the eigenvalue's
@@ -36,8 +37,8 @@
 // Exactness: everything up to a, b, c is integer arithmetic carried in exact containers.  The seven
 // rounding operations of the eigenvalue are separate round-to-nearest operations.  ptxas (12.9) contracts
 // mul.rn.f32x2 + add.rn.f32x2 into FFMA2 even with -fmad=false, so every product whose rounding matters
-// (a*b, c*c, tr*tr) is a scalar __fmul_rn; packed ops are used only where fusing cannot change the
-// result (exact products by 0.5 / 4, sums, the sqrt refinement's intended FMAs).
+// (a*b, c*c, tr*tr) is a scalar operation; packed ops are used only where fusing cannot change the
+// result (FMAs by the exact constants -1 / 4 / 0.5, sums, the sqrt refinement's intended FMAs).
 #include <cuda_fp16.h>
 
 #include <cstdlib>
