@@ -266,6 +266,18 @@ def main():
     e2e_ms = max_over_ranks(1000.0 * (time.perf_counter() - t0) / args.steps)
     barrier()
     clocks = sampler.stop()   # sampled from the first warm-up pass to the end of the end-to-end passes
+    # the floor of the end-to-end step: a bare copy of the same pinned frames to the device (best of 5, CUDA events)
+    src = torch.from_numpy(frames.reshape(-1))
+    dst = torch.empty(src.numel(), dtype=torch.uint8, device="cuda")
+    bare_ms = 1e30
+    for _ in range(5):
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
+        dst.copy_(src, non_blocking=True)
+        ev1.record()
+        ev1.synchronize()
+        bare_ms = min(bare_ms, ev0.elapsed_time(ev1))
+    del dst
     e2e_value = world * n / (e2e_ms / 1000.0)
     h2d = n * ROWS * COLS
     d2h = 4 * n + 8 * n * mk + 4 * (n - 1) + 8 * (n - 1) * mk
@@ -303,6 +315,7 @@ def main():
         "warmup": W, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u8/i32/fp32", "data": "synthetic", "config": workload_config(args, n),
         "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": world * h2d, "d2h_bytes_per_step": world * d2h, "ms_per_step": e2e_ms, "batch": args.e2e_batch,
+                "bare_h2d_copy_ms": bare_ms, "note": "copy-bound: bare_h2d_copy_ms is one cudaMemcpyAsync of the step's frames alone",
                 "timing": "wall clock around the synchronous C-ABI call vo_sequence_run, max over ranks"},
         "gpu_launches": int(launches), "clocks": clocks, "host_binding": numa, "roofline": roofline, "kernel_ms_per_step": kernel_ms,
         "keypoints_per_frame": float(np.mean(nk)), "matches_per_pair": float(np.mean(nm)) if len(nm) else 0.0,
