@@ -333,6 +333,10 @@ def test_large_batches_and_every_segment_count(oracle, monkeypatch):
             assert same(nk, kp, nm, pr), segs
         monkeypatch.delenv("VO_STENCIL_SEGS")
         assert same(*vo.sequence_run(frames, p, 250))
+        assert same(*vo.sequence_run(frames, p, 130))   # last chunk of 130 frames goes in four pieces (65, 32, 16, 17)
+        nk, kp, nm, pr = vo.sequence_run(frames[:100], p, 100)  # a single chunk that is also the last one
+        assert np.array_equal(nk, nk0[:100]) and np.array_equal(nm, nm0[:99])
+        assert all(np.array_equal(pr[k, :nm[k]], pr0[k, :nm[k]]) for k in range(99))
 
 
 def test_errors_are_loud(vo_small):
