@@ -144,7 +144,10 @@ typedef struct vo_seq_result {
 } vo_seq_result;
 
 /* Host frames in, host results out; H2D, kernels and D2H are pipelined over `batch`-frame chunks on
- * separate streams (batch <= n_slots/2). This is the end-to-end path. */
+ * separate streams (batch <= n_slots/2). This is the end-to-end path.  The call is bound by the frame
+ * copy when `frames` and the result arrays are pinned (vo_host_alloc): 1000 KITTI frames take 9.0 ms
+ * against 8.4 ms for the bare copy.  Pageable buffers work but serialise the copies with the host
+ * (measured 14.5 ms with pageable result arrays). */
 int vo_sequence_run(vo_ctx* ctx, const uint8_t* frames, int n_frames, int rows, int cols, size_t pitch,
                     size_t frame_stride, const vo_params* p, int batch, vo_seq_result* out);
 /* Device-resident variant: upload once, then run the kernels only (results stay on the device;
