@@ -20,3 +20,35 @@ def shard_frames(n_frames, rank, world):
     if hi <= lo:
         return lo, lo
     return lo, hi + 1
+
+
+FLIP_Z = (1.0, 1.0, -1.0, 1.0)  # diag of flipZ (PoseUpdate.cpp:7-11); its own inverse
+
+
+def _flip(T):
+    import numpy as np
+    return np.diag(FLIP_Z) @ T
+
+
+def compose_shard_poses(shard_poses):
+    """Stitch per-shard pose lists into the whole trajectory.
+
+    shard_poses[s] is the list of 4x4 poses a shard's driver wrote for its frames [lo_s, hi_s] (hi_s = lo_{s+1}: the
+    shared boundary frame), in the CSV convention of VisualOdometry::run: line 0 is the start pose as it is, every
+    later line is flipZ * T_curr (VisualOdometry.cpp:70,186).  Each shard starts from the identity; the only sequential
+    step of the whole pipeline is the prefix product T_curr = T_curr * T_rel (VisualOdometry.cpp:184), applied here
+    once per shard: G_{s+1} = G_s * T_local_s(last).  Returns the list of poses of frames 0 .. n-1 in the same CSV
+    convention (n = sum of shard lengths - (shards - 1))."""
+    import numpy as np
+    out, G = [], np.eye(4)
+    for s, poses in enumerate(shard_poses):
+        poses = [np.asarray(P, np.float64).reshape(4, 4) for P in poses]
+        if not poses:
+            continue
+        local = [poses[0]] + [_flip(P) for P in poses[1:]]  # un-flipped T_curr per frame
+        first = 0 if not out else 1  # the boundary frame was already emitted by the previous shard
+        for j in range(first, len(local)):
+            T = G @ local[j]
+            out.append(T if (s == 0 and j == 0) or not out else _flip(T))
+        G = G @ local[-1]
+    return out

@@ -27,15 +27,17 @@ def make_canvas(rows, cols, seed=0, n_rects=None):
     return canvas
 
 
-def make_sequence(n_frames, rows=KITTI[0], cols=KITTI[1], seed=0, n_rects=None, noise_sigma=2.0, out=None):
-    """Returns a (n_frames, rows, cols) uint8 array (C-contiguous)."""
+def make_sequence(n_frames, rows=KITTI[0], cols=KITTI[1], seed=0, n_rects=None, noise_sigma=2.0, out=None, start=0):
+    """Returns a (n_frames, rows, cols) uint8 array (C-contiguous): frames start .. start+n_frames-1 of the sequence
+    (a shard of a longer sequence is generated with `start` = its first frame and equals the slice of the whole)."""
     canvas = make_canvas(rows, cols, seed, n_rects).astype(np.float32)
     frames = out if out is not None else np.empty((n_frames, rows, cols), np.uint8)
-    for t in range(n_frames):
+    for k in range(n_frames):
+        t = start + k
         dx, dy = (2 * t) % 32, t % 16
         win = canvas[dy:dy + rows, dx:dx + cols]
         rng = np.random.default_rng([seed, t + 1])
         noise = rng.standard_normal((rows, cols), dtype=np.float32) * np.float32(noise_sigma)
         np.clip(np.rint(win + noise), 0, 255, out=noise)
-        frames[t] = noise.astype(np.uint8)
+        frames[k] = noise.astype(np.uint8)
     return frames

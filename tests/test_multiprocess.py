@@ -60,3 +60,37 @@ def test_two_rank_sharding_reproduces_single_process():
     for p in range(n_frames - 1):
         assert merged[p] == o.match(feats[p][1], feats[p + 1][1], 32).tolist()
     assert sum(len(v) for v in merged.values()) > 0
+
+
+def test_shard_pose_composition_equals_the_unsharded_trajectory():
+    """compose_shard_poses (the one sequential step of the sharded VisualOdometry::run: T_curr = T_curr * T_rel,
+    VisualOdometry.cpp:184) stitches per-shard CSV pose lists into the trajectory a single driver writes; shards of the
+    synthetic sequence equal slices of the whole."""
+    from acs_visual_odometry_b200.shard import compose_shard_poses, shard_frames
+    from acs_visual_odometry_b200.synth import make_sequence
+    whole_frames = make_sequence(6, 60, 80, seed=3, n_rects=20)
+    assert np.array_equal(whole_frames[2:5], make_sequence(3, 60, 80, seed=3, n_rects=20, start=2))
+    rng = np.random.default_rng(0)
+    n = 23
+    rels = []
+    for _ in range(n - 1):
+        th = rng.normal(0, 0.05)
+        T = np.eye(4)
+        T[:3, :3] = [[np.cos(th), 0, np.sin(th)], [0, 1, 0], [-np.sin(th), 0, np.cos(th)]]
+        T[:3, 3] = rng.normal(0, 1, 3)
+        rels.append(T)
+    F = np.diag([1, 1, -1, 1.0])
+
+    def driver(lo, hi):  # poses a driver writes for frames lo..hi: identity, then flipZ * T_curr
+        T, out = np.eye(4), [np.eye(4)]
+        for i in range(lo + 1, hi + 1):
+            T = T @ rels[i - 1]
+            out.append(F @ T)
+        return out
+
+    whole = driver(0, n - 1)
+    for world in (1, 2, 3, 5, 8):
+        shards = [driver(*(lambda lo, hi: (lo, hi - 1))(*shard_frames(n, r, world))) for r in range(world)]
+        got = compose_shard_poses(shards)
+        assert len(got) == n
+        assert max(np.abs(g - w).max() for g, w in zip(got, whole)) < 1e-12
