@@ -59,7 +59,7 @@ HOST_LIB = PKG / "libvohost.so"
 HOST_MAIN = PKG / "vo_main"
 HOST_SOURCES = ["vo_ransac.cpp", "vo_pose.cpp", "vo_image_io.cpp", "vo_pipeline.cpp", "vo_host_abi.cpp"]
 CXX = os.environ.get("CXX", "g++")
-CXXFLAGS = ["-std=c++17", "-O2", "-fPIC", "-ffp-contract=off", "-Wall", "-pthread"]
+CXXFLAGS = ["-std=c++17", "-O3", "-fPIC", "-ffp-contract=off", "-Wall", "-pthread"]
 
 
 def build_host(force=False):

@@ -61,10 +61,14 @@ Mat3 FundamentalMatrix::computeFundamentalMatrix(const std::vector<PointPair>& p
         r[3] = p1(1) * p2(0); r[4] = p1(1) * p2(1); r[5] = p1(1);
         r[6] = p2(0);         r[7] = p2(1);         r[8] = 1.0;
     }
-    double s[9], V[81];
-    jacobi_svd(A.data(), m, 9, s, V);
     Mat3 F;
-    for (int i = 0; i < 9; ++i) F.m[i] = V[i * 9 + 8];  // right singular vector of the smallest singular value
+    if (m == 8) {
+        null_vector_8x9(A.data(), F.m);  // minimal sample: the null vector, without the Jacobi sweeps
+    } else {
+        double s[9], V[81];
+        jacobi_svd(A.data(), m, 9, s, V);
+        for (int i = 0; i < 9; ++i) F.m[i] = V[i * 9 + 8];  // right singular vector of the smallest singular value
+    }
     F = mul(mul(transpose(T2), F), T1);
     // rank 2: zero the smallest singular value
     Mat3 U, W;
@@ -104,28 +108,51 @@ RansacStats Ransac::run(FundamentalMatrix& model, const std::vector<PointPair>& 
     // the reference scores chunks [t*chunk, min(N, (t+1)*chunk)), t < numThreads: the tail N % numThreads is never scored
     const int chunkSize = N / numThreads;
     const int scored = std::min(N, numThreads * chunkSize);
-    std::vector<PointPair> sample, currentInliers;
+    std::vector<PointPair> sample;
+    // scored points as four plain arrays: the scoring loop below has no branch and no store besides the flag
+    std::vector<double> X0(scored), X1(scored), P0(scored), P1(scored);
+    std::vector<unsigned char> flag(scored);
+    for (int i = 0; i < scored; ++i) { X0[i] = data[i].first.x; X1[i] = data[i].first.y; P0[i] = data[i].second.x; P1[i] = data[i].second.y; }
     for (int iter = 0; iter < maxIterations; ++iter) {
         ++st.iterations;
+        // ransac.cpp:142: std::sample = a uniformly random 8-subset in data order.  libstdc++ walks all N elements with
+        // one draw each; Floyd's algorithm draws the same distribution with 8 draws (the reference's generator is
+        // unseeded, so no particular sequence has to be reproduced).
         sample.clear();
-        std::sample(data.begin(), data.end(), std::back_inserter(sample), sampleSize, rng);
+        if (N <= sampleSize) {
+            sample = data;
+        } else {
+            int idx[8], cnt = 0;
+            for (int j = N - sampleSize; j < N; ++j) {
+                const int t = static_cast<int>(std::uniform_int_distribution<int>(0, j)(rng));
+                bool seen = false;
+                for (int q = 0; q < cnt; ++q) seen |= idx[q] == t;
+                idx[cnt++] = seen ? j : t;
+            }
+            std::sort(idx, idx + sampleSize);
+            for (int q = 0; q < sampleSize; ++q) sample.push_back(data[idx[q]]);
+        }
         FundamentalMatrix tempModel;
         tempModel.fit(sample);  // fewer than 8 correspondences: F stays zero, every Sampson error is "max"
         const Mat3 F = tempModel.getMatrix();
-        currentInliers.clear();
+        const double f00 = F(0, 0), f01 = F(0, 1), f02 = F(0, 2), f10 = F(1, 0), f11 = F(1, 1), f12 = F(1, 2), f20 = F(2, 0), f21 = F(2, 1),
+                     f22 = F(2, 2);
+        int count = 0;
         for (int i = 0; i < scored; ++i) {  // computeSampsonError inlined (same operations in the same order)
-            const double x0 = data[i].first.x, x1 = data[i].first.y, p0 = data[i].second.x, p1 = data[i].second.y;
-            const double Fx0 = F(0, 0) * x0 + F(0, 1) * x1 + F(0, 2) * 1.0, Fx1 = F(1, 0) * x0 + F(1, 1) * x1 + F(1, 2) * 1.0,
-                         Fx2 = F(2, 0) * x0 + F(2, 1) * x1 + F(2, 2) * 1.0;
-            const double Ft0 = F(0, 0) * p0 + F(1, 0) * p1 + F(2, 0) * 1.0, Ft1 = F(0, 1) * p0 + F(1, 1) * p1 + F(2, 1) * 1.0;
+            const double x0 = X0[i], x1 = X1[i], p0 = P0[i], p1 = P1[i];
+            const double Fx0 = f00 * x0 + f01 * x1 + f02 * 1.0, Fx1 = f10 * x0 + f11 * x1 + f12 * 1.0, Fx2 = f20 * x0 + f21 * x1 + f22 * 1.0;
+            const double Ft0 = f00 * p0 + f10 * p1 + f20 * 1.0, Ft1 = f01 * p0 + f11 * p1 + f21 * 1.0;
             const double e = p0 * Fx0 + p1 * Fx1 + 1.0 * Fx2;
             const double den = Fx0 * Fx0 + Fx1 * Fx1 + Ft0 * Ft0 + Ft1 * Ft1;
-            if (den < 1e-12) continue;  // error = max
-            if (e * e / den < sampsonThreshold) currentInliers.push_back(data[i]);
+            const unsigned char in = (den >= 1e-12) & (e * e / den < sampsonThreshold);  // den < 1e-12: error = max
+            flag[i] = in;
+            count += in;
         }
-        if (static_cast<int>(currentInliers.size()) > bestInliers) {
-            bestInliers = static_cast<int>(currentInliers.size());
-            bestInlierSet = currentInliers;
+        if (count > bestInliers) {  // the consensus set is materialised only when it is the best so far
+            bestInliers = count;
+            bestInlierSet.clear();
+            for (int i = 0; i < scored; ++i)
+                if (flag[i]) bestInlierSet.push_back(data[i]);
             outlierRatio = 1.0 - static_cast<double>(bestInliers) / N;
             const double denom = std::log(1.0 - std::pow(1.0 - outlierRatio, sampleSize));
             if (denom != 0.0) {
