@@ -93,8 +93,61 @@ void triangulatePoint(const Mat3& R, const Vec3& t, double x1, double y1, double
         A[2 * 4 + j] = x2 * P2[2][j] - P2[0][j];
         A[3 * 4 + j] = y2 * P2[2][j] - P2[1][j];
     }
-    double s[4], V[16];
-    jacobi_svd(A, 4, 4, s, V);
+    // cv::triangulatePoints takes the right singular vector of the smallest singular value of A, i.e. the eigenvector of
+    // the smallest eigenvalue of M = A^T A.  Inverse iteration on the Cholesky factor of M (shifted by 1e-14 trace so
+    // that it stays positive definite when the rays meet exactly) converges by (s4/s3)^2 per step: one or two steps
+    // for inlier correspondences, against ~40 Jacobi rotations.  If it has not converged to 1e-11 after six steps
+    // (rays nearly parallel to the baseline: s4 ~ s3) the Jacobi SVD decides, so the result is the SVD's in every case.
+    double M[4][4];
+    for (int i = 0; i < 4; ++i)
+        for (int j = i; j < 4; ++j) {
+            double acc = 0.0;
+            for (int k = 0; k < 4; ++k) acc += A[k * 4 + i] * A[k * 4 + j];
+            M[i][j] = M[j][i] = acc;
+        }
+    const double shift = 1e-14 * (M[0][0] + M[1][1] + M[2][2] + M[3][3]);
+    double L[4][4] = {};
+    bool ok = shift > 0.0;
+    for (int i = 0; i < 4 && ok; ++i)
+        for (int j = 0; j <= i; ++j) {
+            double acc = M[i][j] + (i == j ? shift : 0.0);
+            for (int k = 0; k < j; ++k) acc -= L[i][k] * L[j][k];
+            if (i == j) { ok = acc > 0.0; L[i][i] = std::sqrt(acc); }
+            else L[i][j] = acc / L[j][j];
+        }
+    if (ok) {
+        const double d[4] = {1.0 / L[0][0], 1.0 / L[1][1], 1.0 / L[2][2], 1.0 / L[3][3]};
+        double x[4] = {0.5, 0.5, 0.5, 0.5};
+        for (int it = 0; it < 6; ++it) {
+            double y[4];
+            for (int i = 0; i < 4; ++i) {  // L z = x
+                double acc = x[i];
+                for (int k = 0; k < i; ++k) acc -= L[i][k] * y[k];
+                y[i] = acc * d[i];
+            }
+            for (int i = 3; i >= 0; --i) {  // L^T y = z
+                double acc = y[i];
+                for (int k = i + 1; k < 4; ++k) acc -= L[k][i] * y[k];
+                y[i] = acc * d[i];
+            }
+            const double nrm = std::sqrt(y[0] * y[0] + y[1] * y[1] + y[2] * y[2] + y[3] * y[3]);
+            if (!(nrm > 0.0) || !std::isfinite(nrm)) break;
+            const double dotp = y[0] * x[0] + y[1] * x[1] + y[2] * x[2] + y[3] * x[3];
+            const double scale = (dotp < 0.0 ? -1.0 : 1.0) / nrm;
+            double change = 0.0;
+            for (int i = 0; i < 4; ++i) {
+                const double v = scale * y[i];
+                change = std::fmax(change, std::fabs(v - x[i]));
+                x[i] = v;
+            }
+            if (it > 0 && change < 1e-11) {  // reaching 1e-11 within six steps needs a ratio (s4/s3)^2 < ~0.02: the remaining error is < 1e-12
+                for (int i = 0; i < 4; ++i) X[i] = x[i];
+                return;
+            }
+        }
+    }
+    double sv[4], V[16];
+    jacobi_svd(A, 4, 4, sv, V);
     for (int i = 0; i < 4; ++i) X[i] = V[i * 4 + 3];
 }
 
