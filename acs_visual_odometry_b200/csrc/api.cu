@@ -31,11 +31,11 @@ int fail_cuda(vo_ctx* c, cudaError_t e, const char* what) {
         ProfRec pr_{(fam), nullptr, nullptr};                        \
         if ((c)->profiling) {                                        \
             cudaEventCreate(&pr_.a); cudaEventCreate(&pr_.b);        \
-            cudaEventRecord(pr_.a, (c)->s_compute);                  \
+            cudaEventRecord(pr_.a, (c)->s_cur);                  \
         }                                                            \
         cudaError_t e_ = (expr);                                     \
         if ((c)->profiling) {                                        \
-            cudaEventRecord(pr_.b, (c)->s_compute);                  \
+            cudaEventRecord(pr_.b, (c)->s_cur);                  \
             (c)->prof.push_back(pr_);                                \
         }                                                            \
         (c)->launches++;                                             \
@@ -67,26 +67,30 @@ int check_geom(vo_ctx* c, int rows, int cols, size_t pitch, size_t min_pitch) {
 int run_extract(vo_ctx* c, const uint8_t* in_base, size_t in_fstride, size_t in_pitch, int n, int rows, int cols,
                 const vo_params* p, int first_slot, bool from_blurred = false, bool stop_after_response = false) {
     const size_t so = (size_t)first_slot;
-    CK(c, cudaMemsetAsync(c->d_cand_count + so, 0, sizeof(int) * n, c->s_compute));
-    CK(c, cudaMemsetAsync(c->d_flags + so, 0, sizeof(int) * n, c->s_compute));
+    CK(c, cudaMemsetAsync(c->d_cand_count + so, 0, sizeof(int) * n, c->s_cur));
+    CK(c, cudaMemsetAsync(c->d_flags + so, 0, sizeof(int) * n, c->s_cur));
     StencilArgs sa;
     sa.in = in_base; sa.in_fstride = in_fstride; sa.in_pitch = in_pitch;
     sa.blur = c->d_blur + so * c->img_fstride; sa.blur_fstride = c->img_fstride; sa.blur_pitch = c->img_pitch;
     sa.R = c->d_R + so * c->r_fstride; sa.R_fstride = c->r_fstride; sa.R_pitch = c->r_pitch;
     sa.rows = rows; sa.cols = cols; sa.threshold = p->threshold;
-    RUN(c, FAM_STENCIL, launch_stencil(sa, n, from_blurred, c->s_compute));
+    RUN(c, FAM_STENCIL, launch_stencil(sa, n, from_blurred, c->s_cur));
     for (int k = 0; k < n; ++k) { c->slot_rows[first_slot + k] = rows; c->slot_cols[first_slot + k] = cols; }
     if (stop_after_response) return VO_OK;
     NmsArgs na;
     na.R = sa.R; na.R_fstride = c->r_fstride; na.R_pitch = c->r_pitch;
     na.cand = c->d_cand + so * c->cand_cap; na.cand_cap = c->cand_cap; na.cand_count = c->d_cand_count + so;
     na.rows = rows; na.cols = cols; na.window = p->nms_window;
-    RUN(c, FAM_NMS, launch_nms(na, n, c->s_compute));
+    RUN(c, FAM_NMS, launch_nms(na, n, c->s_cur));
+    if (c->wait_before_select) {  // resident two-stream schedule: the previous chunk still reads this slot set's boundary frame
+        CK(c, cudaStreamWaitEvent(c->s_cur, c->wait_before_select, 0));
+        c->wait_before_select = nullptr;
+    }
     SelectArgs se;
     se.cand = na.cand; se.cand_cap = c->cand_cap; se.cand_count = na.cand_count;
     se.kp = c->d_kp + so * c->max_kp; se.kp_stride = c->max_kp; se.nkp = c->d_nkp + so; se.flags = c->d_flags + so;
     se.max_keypoints = p->max_keypoints; se.sort_cap = c->sort_cap;
-    RUN(c, FAM_SELECT, launch_select(se, n, c->s_compute));
+    RUN(c, FAM_SELECT, launch_select(se, n, c->s_cur));
     FreakArgs fa;
     fa.blur = from_blurred ? in_base : sa.blur;
     fa.blur_fstride = from_blurred ? in_fstride : c->img_fstride;
@@ -94,7 +98,7 @@ int run_extract(vo_ctx* c, const uint8_t* in_base, size_t in_fstride, size_t in_
     fa.kp = se.kp; fa.kp_stride = c->max_kp; fa.nkp = se.nkp;
     fa.desc = c->d_desc + so * c->max_kp * 16; fa.angles = c->d_angles + so * c->max_kp;
     fa.rows = rows; fa.cols = cols;
-    RUN(c, FAM_FREAK, launch_freak(fa, n, p->max_keypoints, c->s_compute));
+    RUN(c, FAM_FREAK, launch_freak(fa, n, p->max_keypoints, c->s_cur));
     return VO_OK;
 }
 
@@ -106,8 +110,8 @@ int run_match(vo_ctx* c, const int* qslots, const int* tslots, int n_pairs, floa
     ma.partial = c->d_partial; ma.raw = c->d_raw; ma.pairs = pairs_out; ma.nmatch = nmatch_out;
     ma.max_kp = c->max_kp; ma.ratio = ratio; ma.match_bits = match_bits;
     for (int k = 0; k < n_pairs; ++k) { ma.qslot[k] = (short)qslots[k]; ma.tslot[k] = (short)tslots[k]; }
-    RUN(c, FAM_MATCH, launch_match(ma, n_pairs, max_n1, c->s_compute));
-    RUN(c, FAM_FINALIZE, launch_match_finalize(ma, n_pairs, c->s_compute));
+    RUN(c, FAM_MATCH, launch_match(ma, n_pairs, max_n1, c->s_cur));
+    RUN(c, FAM_FINALIZE, launch_match_finalize(ma, n_pairs, c->s_cur));
     return VO_OK;
 }
 
@@ -156,10 +160,10 @@ int run_seq_chunk(vo_ctx* c, const uint8_t* in_base, size_t in_fstride, size_t i
     const int set = (g0 / batch) & 1, base = set * batch;
     int rc = run_extract(c, in_base, in_fstride, in_pitch, cnt, rows, cols, p, base);
     if (rc) return rc;
-    CK(c, cudaMemcpyAsync(c->d_seq_nkp + g0, c->d_nkp + base, sizeof(int) * cnt, cudaMemcpyDeviceToDevice, c->s_compute));
-    CK(c, cudaMemcpyAsync(c->d_seq_flags + g0, c->d_flags + base, sizeof(int) * cnt, cudaMemcpyDeviceToDevice, c->s_compute));
+    CK(c, cudaMemcpyAsync(c->d_seq_nkp + g0, c->d_nkp + base, sizeof(int) * cnt, cudaMemcpyDeviceToDevice, c->s_cur));
+    CK(c, cudaMemcpyAsync(c->d_seq_flags + g0, c->d_flags + base, sizeof(int) * cnt, cudaMemcpyDeviceToDevice, c->s_cur));
     CK(c, cudaMemcpyAsync(c->d_seq_kp + (size_t)g0 * c->max_kp, c->d_kp + (size_t)base * c->max_kp,
-                          sizeof(float2) * (size_t)cnt * c->max_kp, cudaMemcpyDeviceToDevice, c->s_compute));
+                          sizeof(float2) * (size_t)cnt * c->max_kp, cudaMemcpyDeviceToDevice, c->s_cur));
     int qs[VO_MAX_BATCH], ts[VO_MAX_BATCH], np = 0, first_pair = -1;
     for (int g = g0; g < g0 + cnt; ++g) {
         if (g == 0) continue;
@@ -265,6 +269,10 @@ int vo_create(vo_ctx** out, int device, int max_rows, int max_cols, int max_keyp
     c->slot_rows = new int[c->total_slots]();
     c->slot_cols = new int[c->total_slots]();
     CKC(cudaStreamCreateWithFlags(&c->s_compute, cudaStreamNonBlocking));
+    CKC(cudaStreamCreateWithFlags(&c->s_compute2, cudaStreamNonBlocking));
+    c->s_cur = c->s_compute;
+    for (int k = 0; k < 2; ++k) CKC(cudaEventCreateWithFlags(&c->ev_chunk[k], cudaEventDisableTiming));
+    CKC(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
     CKC(cudaStreamCreateWithFlags(&c->s_h2d, cudaStreamNonBlocking));
     CKC(cudaStreamCreateWithFlags(&c->s_d2h, cudaStreamNonBlocking));
     for (int k = 0; k < 2; ++k) {
@@ -302,6 +310,9 @@ void vo_destroy(vo_ctx* c) {
     if (c->ev_t0) cudaEventDestroy(c->ev_t0);
     if (c->ev_t1) cudaEventDestroy(c->ev_t1);
     if (c->s_compute) cudaStreamDestroy(c->s_compute);
+    if (c->s_compute2) cudaStreamDestroy(c->s_compute2);
+    for (int k = 0; k < 2; ++k) if (c->ev_chunk[k]) cudaEventDestroy(c->ev_chunk[k]);
+    if (c->ev_join) cudaEventDestroy(c->ev_join);
     if (c->s_h2d) cudaStreamDestroy(c->s_h2d);
     if (c->s_d2h) cudaStreamDestroy(c->s_d2h);
     delete c;
@@ -615,13 +626,34 @@ int vo_sequence_run_resident(vo_ctx* c, const vo_params* p, int batch) {
     if ((rc = check_params(c, p))) return rc;
     if (batch < 1 || 2 * batch > c->n_slots || batch > VO_MAX_BATCH) return fail(c, VO_ERR_BAD_ARG, "batch must be in 1..n_slots/2");
     CK(c, cudaSetDevice(c->device));
-    for (int g0 = 0; g0 < c->seq_frames; g0 += batch) {
-        const int cnt = c->seq_frames - g0 < batch ? c->seq_frames - g0 : batch;
-        if ((rc = run_seq_chunk(c, c->d_seq + (size_t)g0 * c->seq_fstride, c->seq_fstride, c->seq_pitch, g0, cnt, batch,
-                                c->seq_rows, c->seq_cols, p)))
-            return rc;
+    // Chunks alternate between two streams so that the low-occupancy kernels of one chunk (select, finalize, every
+    // kernel's tail) share the SMs with the stencil / NMS kernels of the next.  Chunk k uses slot set k&1 like chunk
+    // k-2 on the same stream; the one cross-stream hazard is the boundary frame: select(k+1) and freak(k+1) overwrite
+    // the slot set whose last frame match(k) / finalize(k) still read, so select(k+1) waits for chunk k's last
+    // kernel (that also orders the shared matcher scratch).  With per-kernel profiling on, everything stays on one
+    // stream so that the event pairs measure kernels, not overlaps.
+    const bool two = !c->profiling && c->seq_frames > batch;
+    if (two) {  // stream 2 starts after everything already queued on the main stream
+        CK(c, cudaEventRecord(c->ev_join, c->s_compute));
+        CK(c, cudaStreamWaitEvent(c->s_compute2, c->ev_join, 0));
     }
-    return VO_OK;
+    int chunk = 0;
+    rc = VO_OK;
+    for (int g0 = 0; g0 < c->seq_frames && rc == VO_OK; g0 += batch, ++chunk) {
+        const int cnt = c->seq_frames - g0 < batch ? c->seq_frames - g0 : batch;
+        c->s_cur = (two && (chunk & 1)) ? c->s_compute2 : c->s_compute;
+        c->wait_before_select = (two && chunk > 0) ? c->ev_chunk[(chunk - 1) & 1] : nullptr;
+        rc = run_seq_chunk(c, c->d_seq + (size_t)g0 * c->seq_fstride, c->seq_fstride, c->seq_pitch, g0, cnt, batch,
+                           c->seq_rows, c->seq_cols, p);
+        if (rc == VO_OK && two && cudaEventRecord(c->ev_chunk[chunk & 1], c->s_cur) != cudaSuccess) rc = fail(c, VO_ERR_CUDA, "cudaEventRecord");
+    }
+    c->s_cur = c->s_compute;
+    c->wait_before_select = nullptr;
+    if (two) {  // join: whatever follows on the main stream (timer, fetch, the next pass) sees both streams' work
+        if (cudaEventRecord(c->ev_join, c->s_compute2) != cudaSuccess || cudaStreamWaitEvent(c->s_compute, c->ev_join, 0) != cudaSuccess)
+            return fail(c, VO_ERR_CUDA, "stream join");
+    }
+    return rc;
 }
 
 int vo_sequence_fetch(vo_ctx* c, vo_seq_result* out) {

@@ -58,6 +58,11 @@ struct vo_ctx {
     int seq_res_cap = 0;
 
     cudaStream_t s_compute = nullptr, s_h2d = nullptr, s_d2h = nullptr;
+    // Resident sequences alternate their chunks between s_compute and s_compute2 (see vo_sequence_run_resident);
+    // s_cur is the stream run_extract / run_match / run_seq_chunk launch on (s_compute everywhere else).
+    cudaStream_t s_compute2 = nullptr, s_cur = nullptr;
+    cudaEvent_t ev_chunk[2] = {nullptr, nullptr}, ev_join = nullptr;  // chunk k's kernels done (on stream k&1); pass join
+    cudaEvent_t wait_before_select = nullptr;                         // set by the resident path for one run_extract call
     cudaEvent_t ev_h2d[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr}, ev_t0 = nullptr, ev_t1 = nullptr;
     int* h_small = nullptr;  // pinned scratch for counts/flags
     int* h_flags = nullptr; int h_flags_cap = 0;  // pinned per-frame flags of vo_sequence_run
