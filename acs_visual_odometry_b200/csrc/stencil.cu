@@ -156,6 +156,15 @@ __device__ __forceinline__ void shi_tomasi4(const float (&A)[4], const float (&B
     }
 }
 
+// Global stores through an opaque address (the row address is computed once for the three store forms; the opaque
+// register would otherwise turn them into generic-space stores).
+__device__ __forceinline__ void stg_u32(const void* p, uint32_t v) { asm volatile("st.global.b32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+__device__ __forceinline__ void stg_u16(const void* p, uint32_t v) { asm volatile("st.global.b16 [%0], %1;" ::"l"(p), "h"(static_cast<unsigned short>(v)) : "memory"); }
+__device__ __forceinline__ void stg_f2(const void* p, float a, float b) { asm volatile("st.global.v2.f32 [%0], {%1, %2};" ::"l"(p), "f"(a), "f"(b) : "memory"); }
+__device__ __forceinline__ void stg_f4(const void* p, float a, float b, float c, float d) {
+    asm volatile("st.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
 // ---- per-lane history rings ------------------------------------------------------------------------------
 // Layout per warp (bytes): raw rows [8][32] uint2 at 0, blurred rows [8][32] uint2 at 2048, gradient rows
 // [8][32] uint4 at 4096.  Each lane reads back only what it wrote itself; every warp access is one
@@ -351,9 +360,9 @@ k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows, int n_tas
                     const uint32_t b4 = __byte_perm(hE, hO, 0x6240);
                     uint8_t* q = blur_p + j * blur_pitch;
                     asm volatile("" : "+l"(q));  // one address for the three store forms
-                    if (st_full) *reinterpret_cast<uint32_t*>(q) = b4;
-                    if (st_l30) *reinterpret_cast<uint16_t*>(q) = static_cast<uint16_t>(b4);
-                    if (st_l1) *reinterpret_cast<uint16_t*>(q + 2) = static_cast<uint16_t>(b4 >> 16);
+                    if (st_full) stg_u32(q, b4);
+                    if (st_l30) stg_u16(q, b4 & 0xFFFFu);
+                    if (st_l1) stg_u16(q + 2, b4 >> 16);
                 }
                 bE[6 + j] = __hsub2(u2h(hE), k1024);
                 bO[6 + j] = __hsub2(u2h(hO), k1024);
@@ -431,9 +440,9 @@ k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows, int n_tas
                 if (STEADY || orow < ye) {
                     float* q = R_p + j * R_pitch;
                     asm volatile("" : "+l"(q));
-                    if (st_full) *reinterpret_cast<float4*>(q) = make_float4(out[0], out[1], out[2], out[3]);
-                    if (st_l30) *reinterpret_cast<float2*>(q) = make_float2(out[0], out[1]);
-                    if (st_l1) *reinterpret_cast<float2*>(q + 2) = make_float2(out[2], out[3]);
+                    if (st_full) stg_f4(q, out[0], out[1], out[2], out[3]);
+                    if (st_l30) stg_f2(q, out[0], out[1]);
+                    if (st_l1) stg_f2(q + 2, out[2], out[3]);
                 }
             }
         }
