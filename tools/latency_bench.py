@@ -19,12 +19,19 @@ frames = make_sequence(n, 376, 1241, seed=0)
 p = Params.vo_gpu_ref()
 res = {}
 with VoFront(376, 1241, p.max_keypoints, 4) as vo:
-    for mode in ("extract+fetch(desc512)+match", "extract+fetch(packed)+match", "extract+match"):
+    for mode in ("adapter: extract+fetch(desc512)+match_host(desc512)", "extract+fetch(desc512)+match", "extract+fetch(packed)+match", "extract+match"):
         for rep in range(2):
             t0 = time.perf_counter()
             nm = 0
+            prev = None
             for i in range(n):
                 vo.extract(frames[i], p, slot=i & 1)
+                if mode.startswith("adapter"):  # what include/vofront_adapter.hpp does with the reference's vector<vector<uint8_t>> API
+                    _, d512, _ = vo.fetch(i & 1, want_desc512=True, want_packed=False)
+                    if prev is not None:
+                        nm += len(vo.match_host(prev, d512, p.ratio, MATCH_REF32))
+                    prev = d512
+                    continue
                 if mode != "extract+match":
                     vo.fetch(i & 1, want_desc512=mode.startswith("extract+fetch(desc512)"), want_packed=True)
                 if i:
