@@ -247,7 +247,7 @@ int vo_create(vo_ctx** out, int device, int max_rows, int max_cols, int max_keyp
         }                                                                        \
     } while (0)
     CKC(cudaSetDevice(device));
-    CKC(cudaMalloc(&c->d_img, ts * c->img_fstride));
+    CKC(cudaMalloc(&c->d_img, ts * c->img_fstride + 16));  // + the words the stencil reads past an unpadded last row
     CKC(cudaMalloc(&c->d_blur, ts * c->img_fstride));
     CKC(cudaMalloc(&c->d_R, ts * c->r_fstride * sizeof(float)));
     CKC(cudaMalloc(&c->d_cand, ts * c->cand_cap * sizeof(unsigned long long)));
@@ -347,6 +347,14 @@ int vo_extract_batch(vo_ctx* c, const uint8_t* gray, int n, int rows, int cols, 
     if (n > 1 && frame_stride < pitch * (size_t)rows) return fail(c, VO_ERR_BAD_ARG, "frame_stride smaller than a frame");
     CK(c, cudaSetDevice(c->device));
     uint8_t* dst = c->d_img + (size_t)first_slot * c->img_fstride;
+    if (pitch == (size_t)cols) {
+        // unpadded rows: one linear copy per frame, kept in the host layout (the stencil reads any pitch); a strided
+        // 2-D copy of 1241-byte rows costs several times the linear one, most of all from pageable memory
+        for (int k = 0; k < n; ++k)
+            CK(c, cudaMemcpyAsync(dst + (size_t)k * c->img_fstride, gray + (size_t)k * frame_stride, (size_t)rows * cols,
+                                  cudaMemcpyHostToDevice, c->s_compute));
+        return run_extract(c, dst, c->img_fstride, (size_t)cols, n, rows, cols, p, first_slot);
+    }
     for (int k = 0; k < n; ++k)
         CK(c, cudaMemcpy2DAsync(dst + (size_t)k * c->img_fstride, c->img_pitch, gray + (size_t)k * frame_stride, pitch,
                                 (size_t)cols, (size_t)rows, cudaMemcpyHostToDevice, c->s_compute));
