@@ -5,7 +5,8 @@
 // largest by the tuple (R, i, j)) and the manager's std::sort by (int y, int x)
 // (feature_extraction_parallel.cpp:276-282).
 //
-//   k_nms     16-byte loads, four pixels per lane, zero pixels rejected at once; candidates are appended to a
+//   k_nms     16-byte loads, four pixels per lane, zero pixels rejected at once, the non-zero groups of a warp
+//             compacted and tested one per lane; candidates are appended to a
 //             per-frame buffer as 64-bit keys (float bits of R << 32 | i << 16 | j).
 //             R > 0 on every candidate, so the unsigned order of the keys equals the tuple order.
 //   k_select  one CTA per frame: if more than N candidates, an 8-pass MSB radix select finds the N-th
@@ -19,16 +20,21 @@ constexpr int NMS_ROWS = 4;                       // rows per warp (all loads is
 constexpr int NMS_TILE_PX = 8 * NMS_ROWS * 128;   // pixels per CTA: 8 warps x NMS_ROWS rows x 128 columns
 constexpr int NMS_STAGE = NMS_TILE_PX / 4;        // strict maxima are never 8-adjacent: at most one per 2x2 cell
 
-// One warp scans NMS_ROWS row segments of 128 pixels with 16-byte loads, four pixels per lane.  A zero centre
-// can never be a strict maximum (its neighbours are >= 0), so rows of zeros cost one vector load and one
-// compare per four pixels.  Non-zero centres are tested WITHOUT data-dependent loops: the (2h+1) rows of the
-// window are fetched as three aligned float4 each (L1 hits: the neighbouring lanes load the same lines) and the
-// maximum of the window minus its centre is formed with FMNMX; candidate <=> centre > that maximum, which is
-// exactly "no neighbour >= centre" (corner_detection_parallel.cpp:181-190).
+// One warp scans NMS_ROWS row segments of 128 pixels with 16-byte loads, four pixels per lane, all loads issued
+// before the first test.  A zero centre can never be a strict maximum (its neighbours are >= 0), so groups of zeros
+// cost one vector load and a compare.  About one group in twelve holds a non-zero centre, so testing them in place
+// would run the window code with two or three lanes active: instead the warp COMPACTS its non-zero groups (ballot +
+// prefix popcount into a per-warp byte list in shared memory) and hands them out one per lane.  Every item is tested
+// without data-dependent loops: the (2h+1) rows of the window are fetched as three aligned float4 each (L1/L2 hits:
+// the lines were just read) and the maximum of the window minus its centre is formed with FMNMX; candidate <=>
+// centre > that maximum, which is exactly "no neighbour >= centre" (corner_detection_parallel.cpp:181-190).
 // Candidates are staged in shared memory and appended to the frame's list with one global atomic per CTA.
+// (Measured slower: 8 rows per warp; barrier-free warps that pipeline several tiles and append with one global
+// atomic per warp; fetching all window rows up front with shuffled column neighbours: profiles/README.md.)
 template <int HW>
 __global__ void __launch_bounds__(256) k_nms(const NmsArgs a) {
     __shared__ unsigned long long s_keys[NMS_STAGE];
+    __shared__ unsigned char s_item[8][NMS_ROWS * 32];
     __shared__ int s_n, s_base;
     const int f = blockIdx.z;
     const int H = a.rows, W = a.cols;
@@ -37,27 +43,38 @@ __global__ void __launch_bounds__(256) k_nms(const NmsArgs a) {
     const int i_lo = max(h, 35), i_hi = min(H - h - 1, H - 35);
     const int j_lo = max(h, 37), j_hi = min(W - h - 1, W - 37);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int c4 = (j_lo & ~3) + 4 * (blockIdx.x * 32 + lane);  // first of this lane's four columns (16-byte aligned)
+    const int c0 = (j_lo & ~3) + 4 * (blockIdx.x * 32);  // first column of the warp's window (16-byte aligned)
+    const int c4 = c0 + 4 * lane;                        // first of this lane's four columns
     const int i0 = i_lo + (blockIdx.y * 8 + warp) * NMS_ROWS;
     if (threadIdx.x == 0) s_n = 0;
     __syncthreads();
     const float* __restrict__ R = a.R + (size_t)f * a.R_fstride;
-    if (c4 <= j_hi && i0 <= i_hi) {
+    if (i0 <= i_hi) {  // warp-uniform
         float4 v[NMS_ROWS];
 #pragma unroll
         for (int k = 0; k < NMS_ROWS; ++k)
-            v[k] = (i0 + k <= i_hi) ? __ldg(reinterpret_cast<const float4*>(R + (size_t)(i0 + k) * a.R_pitch + c4)) : make_float4(0.f, 0.f, 0.f, 0.f);
+            v[k] = (c4 <= j_hi && i0 + k <= i_hi) ? __ldg(reinterpret_cast<const float4*>(R + (size_t)(i0 + k) * a.R_pitch + c4))
+                                                  : make_float4(0.f, 0.f, 0.f, 0.f);
+        int n = 0;
 #pragma unroll
         for (int k = 0; k < NMS_ROWS; ++k) {
-            const float cv[4] = {v[k].x, v[k].y, v[k].z, v[k].w};
-            if (!(cv[0] > 0.f || cv[1] > 0.f || cv[2] > 0.f || cv[3] > 0.f)) continue;
-            const int i = i0 + k;
+            const bool nz = v[k].x > 0.f || v[k].y > 0.f || v[k].z > 0.f || v[k].w > 0.f;
+            const unsigned b = __ballot_sync(0xFFFFFFFFu, nz);
+            if (nz) s_item[warp][n + __popc(b & ((1u << lane) - 1u))] = (unsigned char)(k * 32 + lane);  // NMS_ROWS * 32 <= 256
+            n += __popc(b);
+        }
+        __syncwarp();
+        for (int t = lane; t < n; t += 32) {
+            const int item = s_item[warp][t];
+            const int i = i0 + (item >> 5), cc = c0 + 4 * (item & 31);
             float m[4] = {0.f, 0.f, 0.f, 0.f};  // max over the window without the centre (all values >= 0)
+            float cv[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
             for (int dn = -h; dn <= h; ++dn) {
-                const float4* row = reinterpret_cast<const float4*>(R + (size_t)(i + dn) * a.R_pitch + c4);
-                const float4 l = __ldg(row - 1), c = dn == 0 ? v[k] : __ldg(row), r = __ldg(row + 1);
-                const float w[12] = {l.x, l.y, l.z, l.w, c.x, c.y, c.z, c.w, r.x, r.y, r.z, r.w};  // columns c4-4 .. c4+7
+                const float4* row = reinterpret_cast<const float4*>(R + (size_t)(i + dn) * a.R_pitch + cc);
+                const float4 l = __ldg(row - 1), c = __ldg(row), r = __ldg(row + 1);
+                const float w[12] = {l.x, l.y, l.z, l.w, c.x, c.y, c.z, c.w, r.x, r.y, r.z, r.w};  // columns cc-4 .. cc+7
+                if (dn == 0) { cv[0] = c.x; cv[1] = c.y; cv[2] = c.z; cv[3] = c.w; }
 #pragma unroll
                 for (int e = 0; e < 4; ++e)
 #pragma unroll
@@ -66,7 +83,7 @@ __global__ void __launch_bounds__(256) k_nms(const NmsArgs a) {
             }
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
-                const int j = c4 + e;
+                const int j = cc + e;
                 if (cv[e] > m[e] && j >= j_lo && j <= j_hi) {  // cv > m >= 0 implies cv > 0
                     const int sp = atomicAdd(&s_n, 1);  // < NMS_STAGE by the 2x2-cell bound
                     s_keys[sp] = ((unsigned long long)__float_as_uint(cv[e]) << 32) | ((unsigned long long)i << 16) | (unsigned long long)j;
