@@ -120,6 +120,13 @@ def test_nms_identical(vo_small, oracle, factory, kitti_pair):
     R[40:160:4, 40:260:4] = 123456.0
     for n in (1, 7, 100, 2000):
         assert np.array_equal(vo_small.nms(R, 3, n), oracle.nms(R, 3, n)), n
+    # dense maps: every 16-byte group of a warp's tile is non-zero, so the compacted item list takes several passes
+    rng = np.random.default_rng(7)
+    dense = rng.uniform(1.0, 1000.0, (200, 300)).astype(np.float32)
+    half = np.where(rng.random((200, 300)) < 0.4, dense, 0.0).astype(np.float32)
+    for R in (dense, half):
+        for k, n in ((5, 500), (7, 2000), (9, 50)):
+            assert np.array_equal(vo_small.nms(R, k, n), oracle.nms(R, k, n)), (k, n)
     # smaller than the safety margins -> nothing
     assert len(vo_small.nms(np.ones((60, 70), np.float32), 5, 10)) == 0
 
