@@ -229,7 +229,7 @@ int vo_create(vo_ctx** out, int device, int max_rows, int max_cols, int max_keyp
     c->cand_cap = VO_CAND_CAP_MIN > 8 * max_keypoints ? VO_CAND_CAP_MIN : 8 * max_keypoints;
     const long long by_area = (long long)max_rows * max_cols / 32;
     if (by_area > c->cand_cap) c->cand_cap = (int)by_area;
-    c->sort_cap = 1;
+    c->sort_cap = 64;  // k_select sorts whole warps' worth (64 keys) in registers
     while (c->sort_cap < max_keypoints) c->sort_cap <<= 1;
     const size_t ts = (size_t)c->total_slots;
     const int pairs_cap = c->total_slots < VO_MAX_BATCH ? c->total_slots : VO_MAX_BATCH;

@@ -154,11 +154,31 @@ __global__ void __launch_bounds__(SEL_NT) k_select(const SelectArgs a) {
     }
     __syncthreads();
     const int n = min(s_count, N);
-    // bitonic sort ascending over the smallest power of two >= n (padding = 0xFFFFFFFF sorts last)
-    int len = 1;
+    // Bitonic sort ascending over the smallest power of two >= max(n, 64) (padding = 0xFFFFFFFF sorts last; sort_cap >= 64).
+    // A thread holds two neighbouring keys, a warp 64: compare distances 1..32 run in registers (the pair itself, then
+    // shuffles), only distances >= 64 go through shared memory with a CTA barrier: 15 barrier stages instead of 66 for
+    // 2048 keys.
+    int len = 64;
     while (len < n) len <<= 1;
-    for (int k = 2; k <= len; k <<= 1)
-        for (int j = k >> 1; j > 0; j >>= 1) {
+    auto warp_stages = [&](uint32_t& x0, uint32_t& x1, int q0, int k, int j_from) {  // distances j_from, j_from/2, .., 1 of phase k
+        const bool up = (q0 & k) == 0;                    // k >= 2: both keys of the thread lie in the same run
+        for (int j = j_from; j >= 2; j >>= 1) {
+            const uint32_t y0 = __shfl_xor_sync(0xFFFFFFFFu, x0, j >> 1), y1 = __shfl_xor_sync(0xFFFFFFFFu, x1, j >> 1);
+            const bool take_min = ((q0 & j) == 0) == up;  // the lower index of the pair keeps the minimum in an ascending run
+            x0 = take_min ? min(x0, y0) : max(x0, y0);
+            x1 = take_min ? min(x1, y1) : max(x1, y1);
+        }
+        const uint32_t lo = min(x0, x1), hi = max(x0, x1);
+        x0 = up ? lo : hi; x1 = up ? hi : lo;
+    };
+    for (int q0 = 2 * tid; q0 < len; q0 += 2 * SEL_NT) {  // warp-uniform: len is a multiple of 64; phases k = 2 .. 64
+        uint2 x = *reinterpret_cast<const uint2*>(s_pos + q0);  // q0 even: 8-byte aligned
+        for (int k = 2; k <= 64; k <<= 1) warp_stages(x.x, x.y, q0, k, k >> 1);
+        *reinterpret_cast<uint2*>(s_pos + q0) = x;
+    }
+    __syncthreads();
+    for (int k = 128; k <= len; k <<= 1) {
+        for (int j = k >> 1; j >= 64; j >>= 1) {
             for (int q = tid; q < len; q += SEL_NT) {
                 const int partner = q ^ j;
                 if (partner > q) {
@@ -169,6 +189,13 @@ __global__ void __launch_bounds__(SEL_NT) k_select(const SelectArgs a) {
             }
             __syncthreads();
         }
+        for (int q0 = 2 * tid; q0 < len; q0 += 2 * SEL_NT) {
+            uint2 x = *reinterpret_cast<const uint2*>(s_pos + q0);
+            warp_stages(x.x, x.y, q0, k, 32);
+            *reinterpret_cast<uint2*>(s_pos + q0) = x;
+        }
+        __syncthreads();
+    }
     float2* __restrict__ kp = a.kp + (size_t)f * a.kp_stride;
     for (int q = tid; q < n; q += SEL_NT) {
         const uint32_t p = s_pos[q];
