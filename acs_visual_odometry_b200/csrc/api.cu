@@ -207,7 +207,7 @@ int vo_create(vo_ctx** out, int device, int max_rows, int max_cols, int max_keyp
     if (max_rows < 1 || max_cols < 1 || max_rows > 32768 || max_cols > 32768)
         return fail(nullptr, VO_ERR_BAD_ARG, "max_rows/max_cols out of range (1..32768)");
     if (max_keypoints < 1 || max_keypoints > 8192) return fail(nullptr, VO_ERR_BAD_ARG, "max_keypoints out of range (1..8192)");
-    if (n_slots < 2 || n_slots > 2 * VO_MAX_BATCH) return fail(nullptr, VO_ERR_BAD_ARG, "n_slots out of range (2..512)");
+    if (n_slots < 2 || n_slots > 2 * VO_MAX_BATCH) return fail(nullptr, VO_ERR_BAD_ARG, "n_slots out of range (2..2*VO_MAX_BATCH = 2048)");
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
         return fail(nullptr, VO_ERR_NO_DEVICE, "no CUDA device: libvofront has no CPU fallback");

@@ -9,7 +9,7 @@
 
 #include "../../include/vofront.h"
 
-#define VO_MAX_BATCH 256       // frames (or pairs) per batched launch
+#define VO_MAX_BATCH 1024       // frames (or pairs) per batched launch
 #define VO_MATCH_SPLITS 8      // train-set slices per query tile (merged by the finalize kernel)
 #define VO_CAND_CAP_MIN 32768  // NMS candidate slots per frame (>= 4 * max_keypoints)
 

@@ -181,7 +181,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--frames", type=int, default=1000)
-    ap.add_argument("--batch", type=int, default=250, help="frames per launch of the resident path (1000 frames = 4 launches; 250 x 11 strips x 3 segments = 8250 stencil tasks, ~3 per resident warp slot)")
+    ap.add_argument("--batch", type=int, default=1000, help="frames per launch of the resident path (library limit 1024). Measured per 1000 frames: batch 250 (4 launches on two alternating streams) 3.19 ms, 500 3.06 ms, 1000 (one launch of each kernel, 11000 stencil tasks) 3.04 ms")
     ap.add_argument("--e2e-batch", type=int, default=100, help="frames per pipelined chunk of vo_sequence_run (copy-bound: 50 and 100 give 9.04 ms per 1000 frames, 200 gives 9.36, 250 gives 9.56 - the last chunk is not overlapped)")
     ap.add_argument("--preset", default="vo_gpu_ref", choices=["vo_gpu_ref", "cpu_ref"])
     ap.add_argument("--match-bits", type=int, default=32, choices=[32, 512])

@@ -70,7 +70,8 @@ int vo_params_preset(vo_params* p, int preset);
  * (feature_extraction_parallel_GPU/corner_detection_parallel_GPU.h:48-52, built in
  * VisualOdometry.cpp:14-23).  All device buffers are sized here; nothing is allocated per frame.
  * n_slots = number of device-resident frame records (image, blurred image, response, candidates,
- * keypoints, packed descriptors); batched calls use consecutive slots modulo n_slots. */
+ * keypoints, packed descriptors), 2 .. 2048; batched calls use consecutive slots modulo n_slots and take at most
+ * 1024 frames (or pairs) per call or chunk. */
 int vo_create(vo_ctx** out, int device, int max_rows, int max_cols, int max_keypoints, int n_slots);
 void vo_destroy(vo_ctx* ctx);
 const char* vo_last_error(const vo_ctx* ctx);

@@ -346,6 +346,33 @@ def test_large_batches_and_every_segment_count(oracle, monkeypatch):
         assert all(np.array_equal(pr[k, :nm[k]], pr0[k, :nm[k]]) for k in range(99))
 
 
+def test_maximum_batch():
+    """1000 frames in one launch of every kernel (the bench's batch; the library's limit is 1024) give the results of
+    100-frame launches and of frame-by-frame extraction, across the chunk boundary too."""
+    from acs_visual_odometry_b200 import Params, VoFront
+    from acs_visual_odometry_b200.synth import make_sequence
+    n = 1010
+    frames = make_sequence(n, 120, 250, seed=35, n_rects=90)
+    p = Params(25000.0, 3, 300)
+    with VoFront(120, 250, 300, 2048) as vo:
+        vo.sequence_upload(frames)
+        vo.sequence_run_resident(p, 1000)
+        nk0, kp0, nm0, pr0 = vo.sequence_fetch()
+        assert nk0.min() > 10 and nm0.min() > 3
+        vo.sequence_run_resident(p, 100)
+        nk, kp, nm, pr = vo.sequence_fetch()
+        assert np.array_equal(nk, nk0) and np.array_equal(nm, nm0)
+        assert all(np.array_equal(kp[k, :nk[k]], kp0[k, :nk[k]]) for k in range(n))
+        assert all(np.array_equal(pr[k, :nm[k]], pr0[k, :nm[k]]) for k in range(n - 1))
+        nk, kp, nm, pr = vo.sequence_run(frames, p, 1024)
+        assert np.array_equal(nk, nk0) and np.array_equal(nm, nm0)
+        assert all(np.array_equal(pr[k, :nm[k]], pr0[k, :nm[k]]) for k in range(n - 1))
+        for k in (0, 511, 999, 1000, 1009):
+            vo.extract(frames[k], p, slot=0)
+            kp1, _, _ = vo.fetch(0)
+            assert np.array_equal(kp0[k, :nk0[k]], kp1), k
+
+
 def test_errors_are_loud(vo_small):
     from acs_visual_odometry_b200 import Params, VoError
     img = np.zeros((100, 120), np.uint8)
