@@ -74,3 +74,14 @@ def test_synth_generator_is_deterministic():
     b = make_sequence(3, 120, 160, seed=5)
     assert a.dtype == np.uint8 and a.shape == (3, 120, 160) and np.array_equal(a, b)
     assert not np.array_equal(a[0], a[1])
+
+
+def test_documented_batch_limits_match_the_library():
+    """include/vofront.h states the slot and batch limits that api.cu enforces (VO_MAX_BATCH in vo_internal.cuh)."""
+    import re
+    root = Path(__file__).resolve().parents[1]
+    m = re.search(r"#define\s+VO_MAX_BATCH\s+(\d+)", (root / "acs_visual_odometry_b200/csrc/vo_internal.cuh").read_text())
+    limit = int(m.group(1))
+    header = (root / "include/vofront.h").read_text()
+    assert f"2 .. {2 * limit}" in header and f"{limit} frames" in header
+    assert f"2*VO_MAX_BATCH = {2 * limit}" in (root / "acs_visual_odometry_b200/csrc/api.cu").read_text()
