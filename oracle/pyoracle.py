@@ -6,6 +6,7 @@ legs.  Two libraries:
   liboracle.so        oracle/vo_oracle.c, the plain-C restatement of the reference hot path
   _ref/libvoref.so    the reference's own TUs compiled unmodified against oracle/shim
                       (built only where /root/reference exists; travels prebuilt to the GPU box)
+  _ref/libvoref_serial.so  the reference's full-length matcher (matching_serial.cpp:24-77), same recipe
 """
 import ctypes as C
 import os
@@ -249,6 +250,36 @@ class Reference:
         if rc:
             raise RuntimeError("voref_bench_sequence failed")
         return dict(extract_s=te.value, match_s=tm.value, keypoints=nk.value, matches=nm.value)
+
+
+class ReferenceSerial:
+    """The reference's own full-length matcher (matching_serial.cpp:24-77 compiled in place into
+    oracle/_ref/libvoref_serial.so, see oracle/ref_serial_driver.cpp): pins the FULL512 mode."""
+
+    def __init__(self):
+        lib = _load(HERE / "_ref" / "libvoref_serial.so")
+        if lib is None:
+            raise RuntimeError("oracle/_ref/libvoref_serial.so missing (needs /root/reference to build)")
+        self.lib = lib
+        lib.voref_serial_hamming.argtypes = [_u8p, _u8p, C.c_int]
+        lib.voref_serial_hamming.restype = C.c_int
+        lib.voref_serial_match.argtypes = [_u8p, C.c_int, _u8p, C.c_int, C.c_int, C.c_float, _i32p, C.c_int]
+        lib.voref_serial_match.restype = C.c_int
+
+    def hamming(self, a, b):
+        a, b = np.ascontiguousarray(a, np.uint8).reshape(-1), np.ascontiguousarray(b, np.uint8).reshape(-1)
+        return self.lib.voref_serial_hamming(a, b, len(a))
+
+    def match(self, d1, d2, ratio=0.75):
+        d1 = np.ascontiguousarray(d1, np.uint8).reshape(-1, 512)
+        d2 = np.ascontiguousarray(d2, np.uint8).reshape(-1, 512)
+        pairs = np.empty((max(d1.shape[0], 1), 2), np.int32)
+        n = self.lib.voref_serial_match(d1, d1.shape[0], d2, d2.shape[0], 512, ratio, pairs, pairs.shape[0])
+        return pairs[:n].copy()
+
+
+def reference_serial_available():
+    return (HERE / "_ref" / "libvoref_serial.so").exists() or Path("/root/reference/matching_serial.cpp").is_file()
 
 
 def reference_available():

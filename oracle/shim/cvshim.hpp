@@ -176,6 +176,7 @@ static inline void GaussianBlur(const Mat& src, Mat& dst, Size ksize, double sig
 
 // ---- display / drawing / misc: no-ops (never reached on the hot path) -------------------------
 static inline void imshow(const std::string&, const Mat&) {}
+template <class... A> static inline void drawMatches(const A&...) {}
 static inline int waitKey(int = 0) { return -1; }
 static inline void destroyAllWindows() {}
 static inline bool imwrite(const std::string&, const Mat&) { return false; }

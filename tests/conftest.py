@@ -30,6 +30,15 @@ def reference():
 
 
 @pytest.fixture(scope="session")
+def reference_serial():
+    """The reference's own full-length matcher (oracle/_ref/libvoref_serial.so); skipped when it was never built."""
+    from oracle import pyoracle
+    if not pyoracle.reference_serial_available():
+        pytest.skip("oracle/_ref/libvoref_serial.so not available")
+    return pyoracle.ReferenceSerial()
+
+
+@pytest.fixture(scope="session")
 def factory():
     import cv2
     f1 = cv2.imread(str(GOLDEN / "factory1.png"), cv2.IMREAD_GRAYSCALE)
@@ -40,12 +49,18 @@ def factory():
 
 @pytest.fixture(scope="session")
 def kitti_pair():
+    """Two KITTI-shaped synthetic frames (synth.make_sequence, seed 7) and the golden vectors the reference's own code
+    produced on them.  The frames are the committed PNGs (tests/golden/kitti{0,1}.png), so the golden comparison never
+    depends on numpy's random stream; a changed generator stream or a corrupt PNG FAILS loudly instead of dropping it."""
     import hashlib
+    import cv2
     from acs_visual_odometry_b200.synth import make_sequence
-    fr = make_sequence(2, seed=7)
     g = dict(np.load(GOLDEN / "kitti_synth.npz"))
-    same = hashlib.sha256(fr.tobytes()).digest() == g["frames_sha256"].tobytes()
-    return fr, (g if same else None)  # None: numpy's generator stream changed; golden comparison not applicable
+    fr = np.stack([cv2.imread(str(GOLDEN / f"kitti{k}.png"), cv2.IMREAD_GRAYSCALE) for k in range(2)])
+    assert fr.shape == (2, 376, 1241) and fr.dtype == np.uint8
+    assert hashlib.sha256(fr.tobytes()).digest() == g["frames_sha256"].tobytes(), "tests/golden/kitti*.png do not match kitti_synth.npz"
+    assert np.array_equal(make_sequence(2, seed=7), fr), "synth.make_sequence(seed=7) no longer reproduces the committed frames"
+    return fr, g
 
 
 @pytest.fixture(scope="session")

@@ -155,9 +155,7 @@ def test_describe_agreement(vo_small, oracle, factory, kitti_pair):
 def test_extract_pipeline_vs_golden(vo_small, factory, kitti_pair):
     from acs_visual_odometry_b200 import Params
     from acs_visual_odometry_b200.api import DBG_ANGLES, DBG_BLURRED, DBG_RESPONSE
-    cases = [(factory[0], factory[2], "factory1"), (factory[1], factory[2], "factory2")]
-    if kitti_pair[1] is not None:
-        cases.append((kitti_pair[0][0], kitti_pair[1], "kitti0"))
+    cases = [(factory[0], factory[2], "factory1"), (factory[1], factory[2], "factory2"), (kitti_pair[0][0], kitti_pair[1], "kitti0")]
     for img, g, tag in cases:
         vo_small.extract(img, Params.cpu_ref(), slot=1)
         kp, d512, packed = vo_small.fetch(1)
@@ -207,10 +205,10 @@ def test_extract_bgr(vo_small, oracle):
 def test_match_known_answers(vo_small, oracle, factory, matcher_kat):
     from acs_visual_odometry_b200 import MATCH_FULL512, MATCH_REF32, matchCustomBinaryDescriptorsThreadPool
     g = factory[2]
-    sets = {"factory": (g["factory1_desc"], g["factory2_desc"], g["factory_matches_ref32"], g["factory_matches_full512_oracle"])}
-    for name in ("random", "ties", "n2_is_1", "n2_is_2", "near_duplicates"):
+    sets = {"factory": (g["factory1_desc"], g["factory2_desc"], g["factory_matches_ref32"], g["factory_matches_full512_ref"])}
+    for name in ("random", "ties", "n2_is_1", "n2_is_2", "near_duplicates", "noisy_duplicates", "prefix_ties"):
         sets[name] = (matcher_kat[f"{name}_d1"], matcher_kat[f"{name}_d2"], matcher_kat[f"{name}_ref32"],
-                      matcher_kat[f"{name}_full512_oracle"])
+                      matcher_kat[f"{name}_full512_ref"])
     for name, (p1, p2, want32, want512) in sets.items():
         for bits, want in ((MATCH_REF32, want32), (MATCH_FULL512, want512)):
             got = vo_small.match_host(p1, p2, 0.75, bits)                       # packed rows
@@ -264,8 +262,9 @@ def test_device_resident_match_equals_host_match(vo_small, oracle, factory):
         got = vo_small.match(3, 4, 0.75, bits)
         assert np.array_equal(got, oracle.match(d1, d2, bits)), bits          # bit-exact given identical descriptors
     m32 = vo_small.match(3, 4, 0.75, MATCH_REF32)
-    print("factory pair: GPU matches", len(m32), "reference 559")
-    assert abs(len(m32) - 559) <= 3
+    # the GPU's descriptors of the factory pair are identical to the reference's, so its match list is the reference's own
+    assert len(m32) == 559 and np.array_equal(m32, factory[2]["factory_matches_ref32"])
+    assert np.array_equal(vo_small.match(3, 4, 0.75, MATCH_FULL512), factory[2]["factory_matches_full512_ref"])
 
 
 def test_batch_and_sequence_equal_single_frames(vo_small, oracle):
@@ -371,6 +370,50 @@ def test_maximum_batch():
             vo.extract(frames[k], p, slot=0)
             kp1, _, _ = vo.fetch(0)
             assert np.array_equal(kp0[k, :nk0[k]], kp1), k
+
+
+def test_bench_shape_vs_oracle(oracle):
+    """The benchmark's own configuration (BASELINE.json configs[1]): 1241x376 frames, preset vo_gpu_ref (20000 / 3 / 2000),
+    vo_sequence_upload + vo_sequence_run_resident with 1000 frames per launch over a 1010-frame sequence, and vo_sequence_run
+    at the end-to-end batch (100).  38 frames spread over the batch (first, middle, last slot 999, the chunk boundary
+    999|1000, the short last chunk) are compared with oracle.extract and 31 pairs with oracle.match: keypoint lists and
+    match lists bit-exact, descriptor bits >= 99.99 %."""
+    from acs_visual_odometry_b200 import Params, VoFront
+    from acs_visual_odometry_b200.synth import make_sequence
+    n = 1010
+    frames = make_sequence(n, seed=0)                       # the bench's sequence (seed 0, rank 0)
+    p = Params.vo_gpu_ref()
+    runs = [range(0, 5), range(123, 127), range(250, 254), range(497, 504), range(747, 752), range(996, 1004), range(1005, 1010)]
+    with VoFront(376, 1241, p.max_keypoints, 2048) as vo:
+        vo.sequence_upload(frames)
+        vo.sequence_run_resident(p, 1000)
+        nk, kp, nm, pr = vo.sequence_fetch()
+        assert 1500 < nk.mean() < 2000 and nm.min() > 100
+        n_frames = n_pairs = n_ident = 0
+        for run in runs:
+            prev = None
+            for f in run:
+                slot = f if f < 1000 else 1000 + (f - 1000)         # chunk 0 -> slots 0..999, chunk 1 -> slots 1000..1009
+                kp_g, d_g, _ = vo.fetch(slot, want_packed=False)
+                kp_o, d_o = oracle.extract(frames[f], p.threshold, p.nms_window, p.max_keypoints)
+                assert nk[f] == len(kp_o) and np.array_equal(kp[f, :nk[f]], kp_o) and np.array_equal(kp_g, kp_o), f
+                assert (d_g == d_o).mean() >= DESC_AGREEMENT_MIN, f
+                n_ident += int(np.array_equal(d_g, d_o))
+                n_frames += 1
+                if prev is not None:                                 # pair (f-1, f): bit-exact given identical descriptors
+                    want = oracle.match(prev[0], d_g, 32, p.ratio)
+                    assert nm[f - 1] == len(want) and np.array_equal(pr[f - 1, :nm[f - 1]], want), f
+                    if prev[1] and np.array_equal(d_g, d_o):         # descriptors identical to the oracle's: the oracle's own list
+                        assert np.array_equal(want, oracle.match(prev[2], d_o, 32, p.ratio))
+                    n_pairs += 1
+                prev = (d_g, np.array_equal(d_g, d_o), d_o)
+        print(f"bench shape: {n_frames} frames / {n_pairs} pairs checked against the oracle, descriptors identical on {n_ident} frames")
+        assert n_frames >= 32 and n_pairs >= 31
+        # the end-to-end entry point at its bench batch gives the same arrays for all 1010 frames
+        nk2, kp2, nm2, pr2 = vo.sequence_run(frames, p, 100)
+        assert np.array_equal(nk2, nk) and np.array_equal(nm2, nm)
+        assert all(np.array_equal(kp2[k, :nk[k]], kp[k, :nk[k]]) for k in range(n))
+        assert all(np.array_equal(pr2[k, :nm[k]], pr[k, :nm[k]]) for k in range(n - 1))
 
 
 def test_errors_are_loud(vo_small):

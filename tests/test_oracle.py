@@ -5,6 +5,8 @@ import pytest
 
 from conftest import dense_R, unpack
 
+KAT_SETS = ("random", "ties", "n2_is_1", "n2_is_2", "near_duplicates", "noisy_duplicates", "prefix_ties")
+
 
 def test_blur_matches_cv2(oracle, factory):
     """cv::GaussianBlur(u8, 7x7, 0) == (sum w w src + 2048) >> 12 with REFLECT_101; cv2 version recorded."""
@@ -32,8 +34,6 @@ def test_oracle_stages_vs_golden_factory(oracle, factory, tag, idx):
 
 def test_oracle_pipeline_vs_golden_kitti(oracle, kitti_pair):
     fr, g = kitti_pair
-    if g is None:
-        pytest.skip("numpy generator stream differs from the one that made the fixture")
     kp0, d0, ang, blurred, R = oracle.extract(fr[0], 25000.0, 5, 1500, stages=True)
     kp1, d1 = oracle.extract(fr[1], 25000.0, 5, 1500)
     assert np.array_equal(blurred, g["kitti0_blurred"])
@@ -49,11 +49,11 @@ def test_oracle_matcher_vs_golden(oracle, factory, matcher_kat):
     d1, d2 = unpack(g["factory1_desc"]), unpack(g["factory2_desc"])
     assert np.array_equal(oracle.match(d1, d2, 32), g["factory_matches_ref32"])
     assert len(g["factory_matches_ref32"]) == 559 and g["factory_matches_ref32"][0].tolist() == [5, 924]
-    assert np.array_equal(oracle.match(d1, d2, 512), g["factory_matches_full512_oracle"])
-    for name in ("random", "ties", "n2_is_1", "n2_is_2", "near_duplicates"):
+    assert np.array_equal(oracle.match(d1, d2, 512), g["factory_matches_full512_ref"])
+    for name in KAT_SETS:
         a, b = unpack(matcher_kat[f"{name}_d1"]), unpack(matcher_kat[f"{name}_d2"])
         assert np.array_equal(oracle.match(a, b, 32), matcher_kat[f"{name}_ref32"]), name
-        assert np.array_equal(oracle.match(a, b, 512), matcher_kat[f"{name}_full512_oracle"]), name
+        assert np.array_equal(oracle.match(a, b, 512), matcher_kat[f"{name}_full512_ref"]), name
 
 
 def test_matcher_semantics(oracle):
@@ -134,6 +134,26 @@ def test_restatement_equals_reference_live(oracle, reference, factory, kitti_pai
     d2[:40] = d1[:40]; d2[:40, rng.integers(0, 32, 40)] ^= 1
     for thr in (1, 3, 8):
         assert np.array_equal(reference.match(d1, d2, threads=thr), oracle.match(d1, d2, 32))
+
+
+def test_full512_restatement_equals_reference_serial_live(oracle, reference_serial, factory, matcher_kat):
+    """Pin of the FULL512 mode: oracle/vo_oracle.c against matching_serial.cpp:24-77 compiled in place
+    (hammingDistance over all 512 bytes, matchCustomBinaryDescriptorsSerial), on the KATs, the factory pair and fresh sets."""
+    g = factory[2]
+    rng = np.random.default_rng(29)
+    a = rng.integers(0, 2, (150, 512), dtype=np.uint8)
+    b = a[rng.permutation(150)][:120].copy()
+    b[rng.random(b.shape) < 0.3] ^= 1                      # distances on both sides of the 0.75 ratio
+    b[:10] = b[10:20]                                       # exact duplicates in the train set: d2 == d1
+    sets = [(unpack(g["factory1_desc"]), unpack(g["factory2_desc"])), (a, b), (a[:1], b), (a, b[:2]), (a, b[:1])]
+    sets += [(unpack(matcher_kat[f"{n}_d1"]), unpack(matcher_kat[f"{n}_d2"])) for n in KAT_SETS]
+    for d1, d2 in sets:
+        for ratio in (0.75, 0.9, 0.5):
+            assert np.array_equal(reference_serial.match(d1, d2, ratio), oracle.match(d1, d2, 512, ratio))
+    _, raw = oracle.match(a, b, 512, raw=True)
+    for q in (0, 7, 149):                                   # best distance of the restatement == the reference's hammingDistance
+        assert raw[q, 0] == reference_serial.hamming(a[q], b[raw[q, 1]])
+        assert raw[q, 0] == min(reference_serial.hamming(a[q], row) for row in b)
 
 
 def test_reference_strip_race_is_avoided_by_single_strip(reference, factory):
