@@ -95,6 +95,7 @@ def load_library():
         "vo_sequence_fetch": (i, [vp, P(_CSeqResult)]),
         "vo_timer_start": (i, [vp]),
         "vo_timer_stop": (i, [vp, P(f)]),
+        "vo_bench_stencil": (i, [vp, P(_CParams), i, i, i, P(f)]),
         "vo_launch_count": (C.c_longlong, [vp, i]),
         "vo_profile_enable": (i, [vp, i]),
         "vo_profile_read": (i, [vp, P(f), P(C.c_longlong), i]),
@@ -311,6 +312,12 @@ class VoFront:
     def timer_stop(self):
         ms = C.c_float()
         self._ck(self.lib.vo_timer_stop(self.h, C.byref(ms)))
+        return ms.value
+
+    def bench_stencil(self, params, batch, fused, reps=5):
+        """Mean ms per launch of the stencil kernel alone over the first `batch` resident frames (see vofront.h)."""
+        ms = C.c_float()
+        self._ck(self.lib.vo_bench_stencil(self.h, C.byref(params.c()), batch, int(bool(fused)), reps, C.byref(ms)))
         return ms.value
 
     def launch_count(self, reset=False):

@@ -3,6 +3,7 @@
 // stencil.cu / nms_select.cu / freak.cu / match.cu.  There is no CPU fallback anywhere: every entry
 // point either runs the CUDA kernels or returns an error code.
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 #include "vo_internal.cuh"
@@ -62,6 +63,15 @@ int check_geom(vo_ctx* c, int rows, int cols, size_t pitch, size_t min_pitch) {
     return VO_OK;
 }
 
+// The response pool [total_slots][max_rows][r_pitch] exists only for the paths that materialise R: the stage entry
+// points vo_response / vo_nms, VO_DBG_RESPONSE, and extraction with NMS windows 7 / 9 or on images too small for a
+// candidate.  The fused extraction path never writes R, so the pool is allocated on first use.
+int ensure_R(vo_ctx* c) {
+    if (c->d_R) return VO_OK;
+    CK(c, cudaMalloc(&c->d_R, (size_t)c->total_slots * c->r_fstride * sizeof(float)));
+    return VO_OK;
+}
+
 // All stages for n frames whose gray images are at in_base + k*in_fstride; results go to slots
 // first_slot .. first_slot+n-1.  Asynchronous on s_compute.
 int run_extract(vo_ctx* c, const uint8_t* in_base, size_t in_fstride, size_t in_pitch, int n, int rows, int cols,
@@ -69,19 +79,28 @@ int run_extract(vo_ctx* c, const uint8_t* in_base, size_t in_fstride, size_t in_
     const size_t so = (size_t)first_slot;
     CK(c, cudaMemsetAsync(c->d_cand_count + so, 0, sizeof(int) * n, c->s_cur));
     CK(c, cudaMemsetAsync(c->d_flags + so, 0, sizeof(int) * n, c->s_cur));
+    // Fused path: the stencil kernel keeps the response on chip and appends the NMS candidates itself (no R round trip).
+    const bool fused = !from_blurred && !stop_after_response && !c->force_unfused && stencil_can_fuse(rows, cols, p->nms_window);
+    int rc_;
+    if (!fused && (rc_ = ensure_R(c))) return rc_;
     StencilArgs sa;
     sa.in = in_base; sa.in_fstride = in_fstride; sa.in_pitch = in_pitch;
     sa.blur = c->d_blur + so * c->img_fstride; sa.blur_fstride = c->img_fstride; sa.blur_pitch = c->img_pitch;
-    sa.R = c->d_R + so * c->r_fstride; sa.R_fstride = c->r_fstride; sa.R_pitch = c->r_pitch;
+    sa.R = fused ? nullptr : c->d_R + so * c->r_fstride; sa.R_fstride = c->r_fstride; sa.R_pitch = c->r_pitch;
     sa.rows = rows; sa.cols = cols; sa.threshold = p->threshold;
-    RUN(c, FAM_STENCIL, launch_stencil(sa, n, from_blurred, c->s_cur));
-    for (int k = 0; k < n; ++k) { c->slot_rows[first_slot + k] = rows; c->slot_cols[first_slot + k] = cols; }
+    sa.nms_h = fused ? p->nms_window / 2 : 0;
+    sa.cand = c->d_cand + so * c->cand_cap; sa.cand_cap = c->cand_cap; sa.cand_count = c->d_cand_count + so;
+    RUN(c, FAM_STENCIL, launch_stencil(sa, n, from_blurred ? STENCIL_SRC_BLURRED : STENCIL_SRC_GRAY, c->s_cur));
+    for (int k = 0; k < n; ++k) {
+        c->slot_rows[first_slot + k] = rows; c->slot_cols[first_slot + k] = cols;
+        c->slot_thr[first_slot + k] = p->threshold; c->slot_has_R[first_slot + k] = !fused;
+    }
     if (stop_after_response) return VO_OK;
     NmsArgs na;
     na.R = sa.R; na.R_fstride = c->r_fstride; na.R_pitch = c->r_pitch;
-    na.cand = c->d_cand + so * c->cand_cap; na.cand_cap = c->cand_cap; na.cand_count = c->d_cand_count + so;
+    na.cand = sa.cand; na.cand_cap = c->cand_cap; na.cand_count = sa.cand_count;
     na.rows = rows; na.cols = cols; na.window = p->nms_window;
-    RUN(c, FAM_NMS, launch_nms(na, n, c->s_cur));
+    if (!fused) RUN(c, FAM_NMS, launch_nms(na, n, c->s_cur));
     if (c->wait_before_select) {  // resident two-stream schedule: the previous chunk still reads this slot set's boundary frame
         CK(c, cudaStreamWaitEvent(c->s_cur, c->wait_before_select, 0));
         c->wait_before_select = nullptr;
@@ -249,7 +268,6 @@ int vo_create(vo_ctx** out, int device, int max_rows, int max_cols, int max_keyp
     CKC(cudaSetDevice(device));
     CKC(cudaMalloc(&c->d_img, ts * c->img_fstride + 16));  // + the words the stencil reads past an unpadded last row
     CKC(cudaMalloc(&c->d_blur, ts * c->img_fstride));
-    CKC(cudaMalloc(&c->d_R, ts * c->r_fstride * sizeof(float)));
     CKC(cudaMalloc(&c->d_cand, ts * c->cand_cap * sizeof(unsigned long long)));
     CKC(cudaMalloc(&c->d_cand_count, ts * sizeof(int)));
     CKC(cudaMalloc(&c->d_kp, ts * max_keypoints * sizeof(float2)));
@@ -268,6 +286,9 @@ int vo_create(vo_ctx** out, int device, int max_rows, int max_cols, int max_keyp
     CKC(cudaMallocHost(&c->h_small, sizeof(int) * 4 * (2 * VO_MAX_BATCH + 8)));
     c->slot_rows = new int[c->total_slots]();
     c->slot_cols = new int[c->total_slots]();
+    c->slot_thr = new float[c->total_slots]();
+    c->slot_has_R = new bool[c->total_slots]();
+    if (const char* e = getenv("VO_FORCE_UNFUSED")) c->force_unfused = e[0] == '1';  // test / measurement aid: R round trip + k_nms
     CKC(cudaStreamCreateWithFlags(&c->s_compute, cudaStreamNonBlocking));
     CKC(cudaStreamCreateWithFlags(&c->s_compute2, cudaStreamNonBlocking));
     c->s_cur = c->s_compute;
@@ -302,7 +323,7 @@ void vo_destroy(vo_ctx* c) {
     cudaFree(c->d_seq_flags); cudaFree(c->d_stage);
     if (c->h_small) cudaFreeHost(c->h_small);
     if (c->h_flags) cudaFreeHost(c->h_flags);
-    delete[] c->slot_rows; delete[] c->slot_cols;
+    delete[] c->slot_rows; delete[] c->slot_cols; delete[] c->slot_thr; delete[] c->slot_has_R;
     for (int k = 0; k < 2; ++k) {
         if (c->ev_h2d[k]) cudaEventDestroy(c->ev_h2d[k]);
         if (c->ev_done[k]) cudaEventDestroy(c->ev_done[k]);
@@ -415,6 +436,20 @@ int vo_debug_fetch(vo_ctx* c, int slot, int what, void* dst) {
         CK(c, cudaMemcpy2DAsync(dst, (size_t)cols, c->d_blur + (size_t)slot * c->img_fstride, c->img_pitch, (size_t)cols,
                                 (size_t)rows, cudaMemcpyDeviceToHost, c->s_compute));
     } else if (what == VO_DBG_RESPONSE) {
+        int rc;
+        if ((rc = ensure_R(c))) return rc;
+        if (!c->slot_has_R[slot]) {
+            // the fused extraction never materialised R: recompute it from the slot's blurred image with the writing form
+            // of the same kernel (same arithmetic), at the threshold the slot was extracted with
+            StencilArgs sa;
+            sa.in = c->d_blur + (size_t)slot * c->img_fstride; sa.in_fstride = c->img_fstride; sa.in_pitch = c->img_pitch;
+            sa.blur = nullptr; sa.blur_fstride = c->img_fstride; sa.blur_pitch = c->img_pitch;
+            sa.R = c->d_R + (size_t)slot * c->r_fstride; sa.R_fstride = c->r_fstride; sa.R_pitch = c->r_pitch;
+            sa.rows = rows; sa.cols = cols; sa.threshold = c->slot_thr[slot];
+            sa.nms_h = 0; sa.cand = nullptr; sa.cand_cap = 0; sa.cand_count = nullptr;
+            RUN(c, FAM_STENCIL, launch_stencil(sa, 1, STENCIL_SRC_BLURRED, c->s_compute));
+            c->slot_has_R[slot] = true;
+        }
         CK(c, cudaMemcpy2DAsync(dst, (size_t)cols * 4, c->d_R + (size_t)slot * c->r_fstride, c->r_pitch * 4, (size_t)cols * 4,
                                 (size_t)rows, cudaMemcpyDeviceToHost, c->s_compute));
     } else if (what == VO_DBG_ANGLES) {
@@ -466,6 +501,7 @@ int vo_nms(vo_ctx* c, const float* R, int rows, int cols, int nms_window, int ma
     int rc;
     if ((rc = check_params(c, &p)) || (rc = check_geom(c, rows, cols, (size_t)cols, (size_t)cols))) return rc;
     CK(c, cudaSetDevice(c->device));
+    if ((rc = ensure_R(c))) return rc;
     const int slot = c->n_slots;
     const size_t so = (size_t)slot;
     CK(c, cudaMemcpy2DAsync(c->d_R + so * c->r_fstride, c->r_pitch * 4, R, (size_t)cols * 4, (size_t)cols * 4, (size_t)rows,
@@ -476,7 +512,19 @@ int vo_nms(vo_ctx* c, const float* R, int rows, int cols, int nms_window, int ma
     na.R = c->d_R + so * c->r_fstride; na.R_fstride = c->r_fstride; na.R_pitch = c->r_pitch;
     na.cand = c->d_cand + so * c->cand_cap; na.cand_cap = c->cand_cap; na.cand_count = c->d_cand_count + so;
     na.rows = rows; na.cols = cols; na.window = nms_window;
-    RUN(c, FAM_NMS, launch_nms(na, 1, c->s_compute));
+    if (!c->force_unfused && stencil_can_fuse(rows, cols, nms_window)) {
+        // windows 3 and 5: the map is streamed through the suppression code of the fused stencil kernel, i.e. the code
+        // the extraction path runs (the stand-alone k_nms serves windows 7 / 9 and VO_FORCE_UNFUSED)
+        StencilArgs sa;
+        sa.in = nullptr; sa.in_fstride = 0; sa.in_pitch = 0;
+        sa.blur = nullptr; sa.blur_fstride = c->img_fstride; sa.blur_pitch = c->img_pitch;
+        sa.R = c->d_R + so * c->r_fstride; sa.R_fstride = c->r_fstride; sa.R_pitch = c->r_pitch;
+        sa.rows = rows; sa.cols = cols; sa.threshold = 0.f;
+        sa.nms_h = nms_window / 2; sa.cand = na.cand; sa.cand_cap = c->cand_cap; sa.cand_count = na.cand_count;
+        RUN(c, FAM_STENCIL, launch_stencil(sa, 1, STENCIL_SRC_RESPONSE, c->s_compute));
+    } else {
+        RUN(c, FAM_NMS, launch_nms(na, 1, c->s_compute));
+    }
     SelectArgs se;
     se.cand = na.cand; se.cand_cap = c->cand_cap; se.cand_count = na.cand_count;
     se.kp = c->d_kp + so * c->max_kp; se.kp_stride = c->max_kp; se.nkp = c->d_nkp + so; se.flags = c->d_flags + so;
@@ -763,6 +811,43 @@ int vo_timer_stop(vo_ctx* c, float* ms) {
     CK(c, cudaEventElapsedTime(ms, c->ev_t0, c->ev_t1));
     return VO_OK;
 }
+int vo_bench_stencil(vo_ctx* c, const vo_params* p, int batch, int mode, int reps, float* ms_per_launch) {
+    if (!c) return VO_ERR_BAD_ARG;
+    if (!ms_per_launch || reps < 1) return fail(c, VO_ERR_BAD_ARG, "bad arguments");
+    if (c->seq_frames < 1) return fail(c, VO_ERR_STATE, "no sequence uploaded");
+    int rc;
+    if ((rc = check_params(c, p))) return rc;
+    if (batch < 1 || batch > c->n_slots || batch > VO_MAX_BATCH || batch > c->seq_frames)
+        return fail(c, VO_ERR_BAD_ARG, "batch must be in 1..min(n_slots, frames uploaded)");
+    const bool fused = mode == 1;
+    if (mode != 0 && mode != 1) return fail(c, VO_ERR_BAD_ARG, "mode must be 0 (write R) or 1 (fused NMS)");
+    if (fused && !stencil_can_fuse(c->seq_rows, c->seq_cols, p->nms_window)) return fail(c, VO_ERR_BAD_ARG, "this geometry / window has no fused form");
+    CK(c, cudaSetDevice(c->device));
+    if (!fused && (rc = ensure_R(c))) return rc;
+    StencilArgs sa;
+    sa.in = c->d_seq; sa.in_fstride = c->seq_fstride; sa.in_pitch = c->seq_pitch;
+    sa.blur = c->d_blur; sa.blur_fstride = c->img_fstride; sa.blur_pitch = c->img_pitch;
+    sa.R = fused ? nullptr : c->d_R; sa.R_fstride = c->r_fstride; sa.R_pitch = c->r_pitch;
+    sa.rows = c->seq_rows; sa.cols = c->seq_cols; sa.threshold = p->threshold;
+    sa.nms_h = fused ? p->nms_window / 2 : 0; sa.cand = c->d_cand; sa.cand_cap = c->cand_cap; sa.cand_count = c->d_cand_count;
+    float total = 0.f;
+    for (int r = 0; r < reps; ++r) {
+        CK(c, cudaMemsetAsync(c->d_cand_count, 0, sizeof(int) * batch, c->s_compute));
+        CK(c, cudaEventRecord(c->ev_t0, c->s_compute));
+        cudaError_t e = launch_stencil(sa, batch, STENCIL_SRC_GRAY, c->s_compute);
+        c->launches++;
+        if (e != cudaSuccess) return fail_cuda(c, e, "launch_stencil");
+        CK(c, cudaEventRecord(c->ev_t1, c->s_compute));
+        CK(c, cudaEventSynchronize(c->ev_t1));
+        float ms = 0.f;
+        CK(c, cudaEventElapsedTime(&ms, c->ev_t0, c->ev_t1));
+        total += ms;
+    }
+    for (int k = 0; k < batch; ++k) { c->slot_rows[k] = 0; c->slot_has_R[k] = false; }  // the slots hold no complete frame record
+    *ms_per_launch = total / reps;
+    return VO_OK;
+}
+
 long long vo_launch_count(vo_ctx* c, int reset) {
     if (!c) return -1;
     const long long v = c->launches;

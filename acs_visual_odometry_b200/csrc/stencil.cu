@@ -51,6 +51,12 @@ namespace {
 constexpr int SW = 116;    // output columns per warp strip: the 128-pixel window minus 6 halo columns each side
 constexpr int HX = 8;      // window start relative to strip*SW (6 halo columns needed; 8 keeps the 4-pixel groups aligned,
                            // so lane 1 stores only its upper two pixels and lane 30 only its lower two)
+// Fused-NMS mode (the response never leaves the SM): strips advance by 112 columns and start at strip*112 - 4.
+// Window columns 3..124 hold valid blurred pixels, 6..121 valid responses, and the NMS centres a strip owns are its
+// lanes 2..29 (window columns 8..119): their k x k windows (k <= 5) stay inside columns 6..121.  Blurred pixels are
+// stored by lanes 1..28 (whole 4-pixel groups only); the last strip also stores lanes 29..31 up to the image edge.
+constexpr int SWF = 112;
+constexpr int HXF = 4;
 // One warp per CTA, 20 CTAs per SM (96 registers): warps are independent tasks, so single-warp CTAs let the block
 // scheduler spread a partly filled wave evenly over the SMs (550 four-warp CTAs left some SMs with 16 and some with
 // 12 warps).  Measured per 1000 KITTI frames at batch 200: 4x4 1.267 ms, 1x16 1.312, 3x6 1.277, 1x18 1.212, 1x20 1.200.
@@ -63,6 +69,10 @@ constexpr int RB = 4;      // rows per loop trip; must divide the ring length 8
 #define VO_CTAS 20
 #endif
 constexpr int CTAS_PER_SM = VO_CTAS;
+#ifndef VO_CTAS_FUSED
+#define VO_CTAS_FUSED 17
+#endif
+constexpr int CTAS_PER_SM_FUSED = VO_CTAS_FUSED;  // 12.4 KB of rings per warp (+ 1 KB the system reserves per CTA)
 constexpr unsigned FULL = 0xFFFFFFFFu;
 typedef unsigned long long u64;
 
@@ -172,6 +182,11 @@ __device__ __forceinline__ void stg_f4(const void* p, float a, float b, float c,
 // (c & 7) ^ (t0 & 4): slots 0-3 relative to one base pointer and 4-7 relative to the other, the two bases
 // swapping every trip.
 constexpr int RING_BYTES = 8192;
+// Fused-NMS mode adds a ring of the last eight thresholded response rows, [8][32] float4 at 8192 (every lane may read
+// every lane's pixels: the window test of a compacted item needs its neighbours' columns), and the item list of a trip
+// (one byte per non-zero 4-pixel group: row-in-trip * 32 + lane) at 12288.
+constexpr int RRING_OFF = 8192, ITEM_OFF = 12288;
+constexpr int RING_BYTES_FUSED = 12288 + 128;
 __device__ __forceinline__ const char* slot_of(const char* pa, const char* pb, int c, int row_bytes) {
     const int s = c & 7;
     return ((s & 4) ? pb : pa) + (s & 3) * row_bytes;
@@ -183,10 +198,17 @@ __device__ __forceinline__ void sts4(const char* p, uint4 v) { *reinterpret_cast
 
 // GATHER: every lane fetches its four (reflected) bytes itself, synchronously: any image size, used for
 // images too small for the mirror scheme.  ALIGNED: rows start on 4-byte boundaries (one load per row).
-template <bool FROM_BLURRED, bool GATHER, bool ALIGNED>
-__global__ void __launch_bounds__(32 * NWARP, CTAS_PER_SM)
+// NMSH = 0: the thresholded response is written to a.R (vo_response, VO_DBG_RESPONSE, windows 7 and 9, tiny images).
+// NMSH = 1, 2: fused non-maximum suppression with half window NMSH (corner_detection_parallel.cpp:166-208): the response
+// stays in the warp's shared-memory ring and only candidate keys leave the SM (2 B/px + 8 B per candidate).
+// SRC = 0: gray input; 1: blurred input (vo_response); 2: a thresholded response map is streamed through the fused NMS
+// instead of being computed (vo_nms with windows 3 / 5: the suppression code under test is the production code).
+template <int SRC, bool GATHER, bool ALIGNED, int NMSH>
+__global__ void __launch_bounds__(32 * NWARP, NMSH ? CTAS_PER_SM_FUSED : CTAS_PER_SM)
 k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows, int n_tasks) {
-    __shared__ __align__(16) char s_rings[NWARP][RING_BYTES];
+    constexpr bool FUSED = NMSH > 0, FROM_BLURRED = SRC == 1, FROM_R = SRC == 2;
+    static_assert(!FROM_R || FUSED, "a response map can only feed the fused NMS");
+    __shared__ __align__(16) char s_rings[NWARP][FUSED ? RING_BYTES_FUSED : RING_BYTES];
     const int lane = threadIdx.x & 31;
     // tasks = (frame, row segment, strip), numbered across the whole batch so that no warp slot of a CTA idles
     const int gtask = blockIdx.x * NWARP + (threadIdx.x >> 5);
@@ -196,15 +218,19 @@ k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows, int n_tas
     const int f = gtask / per_frame, task = gtask - f * per_frame;
     const int strip = task % n_strips, seg = task / n_strips;
     const int H = a.rows, W = a.cols;
-    const int ys = seg * seg_rows, ye = min(H, ys + seg_rows);
-    const int xs = strip * SW - HX;
+    // rows this task owns (blurred rows it stores, NMS centres it decides) and rows it computes: a fused segment also
+    // computes the four response rows either side of its own (its windows reach NMSH <= 2 rows across the border)
+    const int ys_own = seg * seg_rows, ye_own = min(H, ys_own + seg_rows);
+    const int ys = FUSED ? max(0, ys_own - RB) : ys_own, ye = FUSED ? min(H, ye_own + RB) : ye_own;
+    const int xs = FUSED ? strip * SWF - HXF : strip * SW - HX;
     const int x = xs + 4 * lane;  // this lane's columns: x .. x+3
-    // outputs of this strip: columns xs+6 .. xs+121, i.e. lanes 2..29 whole, lane 1 pixels 2-3, lane 30 pixels 0-1
-    // lanes 2..29 store their four pixels, lane 1 its upper pair, lane 30 its lower pair
-    const bool st_full = lane >= 2 && lane < 30 && x < W, st_l1 = lane == 1 && x + 2 >= 0 && x + 2 < W, st_l30 = lane == 30 && x < W;
+    // unfused: outputs of this strip are columns xs+6 .. xs+121: lanes 2..29 store their four pixels, lane 1 its upper
+    // pair, lane 30 its lower pair.  Fused: blurred pixels only, whole groups, lanes 1..28 (to the image edge on the last strip)
+    const bool st_full = FUSED ? (lane >= 1 && (lane <= 28 || strip == n_strips - 1) && x < W) : (lane >= 2 && lane < 30 && x < W);
+    const bool st_l1 = !FUSED && lane == 1 && x + 2 >= 0 && x + 2 < W, st_l30 = !FUSED && lane == 30 && x < W;
     const uint8_t* __restrict__ in = a.in + (size_t)f * a.in_fstride;
-    uint8_t* __restrict__ blur_out = FROM_BLURRED ? nullptr : a.blur + (size_t)f * a.blur_fstride;
-    float* __restrict__ R = a.R + (size_t)f * a.R_fstride;
+    uint8_t* __restrict__ blur_out = (FROM_BLURRED || FROM_R) ? nullptr : a.blur + (size_t)f * a.blur_fstride;
+    float* __restrict__ R = (FUSED && !FROM_R) ? nullptr : a.R + (size_t)f * a.R_fstride;
     const float thr = a.threshold;
     const float kInf = __int_as_float(0x7f800000);
 
@@ -279,6 +305,18 @@ k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows, int n_tas
         sts4(ja + k * 512, make_uint4(0u, 0u, 0u, 0u)); sts4(jb + k * 512, make_uint4(0u, 0u, 0u, 0u));
     }
     float sa[4] = {0.f, 0.f, 0.f, 0.f}, sb[4] = {0.f, 0.f, 0.f, 0.f};  // running 5-row sums of Jx^2, Jy^2 per pixel
+    // fused NMS state: the response ring (slot of step t = t & 7, absolute), the non-zero masks of the last NMSH rows of
+    // the previous trip, the centre rows / columns this task decides and the frame's candidate list
+    char* const rring = ring + RRING_OFF;
+    unsigned char* const s_item = reinterpret_cast<unsigned char*>(ring + ITEM_OFF);
+    unsigned nz_prev[2] = {0u, 0u};
+    const int nms_i_lo = max(max(NMSH, 35), ys_own), nms_i_hi = min(min(H - NMSH - 1, H - 35), ye_own - 1);
+    const int nms_j_lo = max(NMSH, 37), nms_j_hi = min(W - NMSH - 1, W - 37);
+    unsigned long long* __restrict__ cand = FUSED ? a.cand + (size_t)f * a.cand_cap : nullptr;
+    if (FUSED) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) sts4(rring + k * 512 + lane * 16, make_uint4(0u, 0u, 0u, 0u));
+    }
 
     const __half2 hz = __floats2half2_rn(0.f, 0.f), two = __floats2half2_rn(2.f, 2.f), k1024 = __floats2half2_rn(1024.f, 1024.f);
 
@@ -287,12 +325,95 @@ k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows, int n_tas
     const int T = (ye - ys) + 12;
     const int r0 = ys - 6;
     const int load_off = FROM_BLURRED ? -3 : 0;
-    issue(r0 + load_off, false);
+    if (!FROM_R) issue(r0 + load_off, false);
     in_next += (long long)(r0 + RB + load_off) * in_pitch;  // trip t0 requests rows r0+t0+RB+load_off ..
     // output row pointers of step t0 (this lane's column), advanced by RB rows per trip
     const long long blur_pitch = (long long)a.blur_pitch, R_pitch = (long long)a.R_pitch;
-    uint8_t* blur_p = FROM_BLURRED ? nullptr : blur_out + (long long)(r0 - 3) * blur_pitch + x;
-    float* R_p = R + (long long)(r0 - 6) * R_pitch + x;
+    uint8_t* blur_p = (FROM_BLURRED || FROM_R) ? nullptr : blur_out + (long long)(r0 - 3) * blur_pitch + x;
+    float* R_p = FUSED ? nullptr : R + (long long)(r0 - 6) * R_pitch + x;
+
+    // ---- fused NMS: one trip's centre rows -------------------------------------------------------------------
+    // Called after the response rows of steps t0 .. t0+3 are in the ring (nz[j] = lanes whose group of row j is not all
+    // zero).  The centre rows o0-h .. o0+3-h have complete windows now.  A zero centre can never be a strict maximum, so
+    // only non-zero groups are tested: the warp compacts them (ballot masks -> byte list in shared memory) and hands
+    // them out one per lane, like k_nms does from global memory.
+    auto nms_trip = [&](const int t0, const unsigned (&nz)[RB]) {
+        // ---- 5. non-maximum suppression of the centre rows o0-h .. o0+3-h (their windows are complete now) ---
+        constexpr int h = NMSH > 0 ? NMSH : 1;
+        const int o0 = r0 + t0 - 6;  // response row of step t0
+        unsigned M[RB];              // non-zero groups per centre row: lanes 2..29 own the centres
+#pragma unroll
+        for (int k = 0; k < RB; ++k) {
+            const unsigned m = k < h ? nz_prev[2 - h + k] : nz[k - h];
+            const int i = o0 - h + k;
+            M[k] = (i >= nms_i_lo && i <= nms_i_hi) ? (m & 0x3FFFFFFCu) : 0u;
+        }
+        nz_prev[0] = nz[2]; nz_prev[1] = nz[3];
+        const int total = __popc(M[0]) + __popc(M[1]) + __popc(M[2]) + __popc(M[3]);
+        if (total > 0) {  // warp-uniform
+            // compact the non-zero groups into the item list, one byte each: centre row k * 32 + lane
+            const unsigned lt = (1u << lane) - 1u;
+            int cum = 0;
+#pragma unroll
+            for (int k = 0; k < RB; ++k) {
+                if ((M[k] >> lane) & 1u) s_item[cum + __popc(M[k] & lt)] = (unsigned char)(k * 32 + lane);
+                cum += __popc(M[k]);
+            }
+            __syncwarp();  // ring rows and item list written by other lanes are visible from here on
+            for (int base = 0; base < total; base += 32) {
+                const int e = base + lane;
+                const bool live = e < total;
+                const int item = live ? (int)s_item[e] : 2;  // idle lanes test a harmless in-range item
+                const int k = item >> 5, l = item & 31;
+                // window rows = steps t0 + k - 2h .. t0 + k, columns 4l - h .. 4l + 3 + h (contiguous in the ring)
+                float m4[4] = {0.f, 0.f, 0.f, 0.f}, cv[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                for (int d = 0; d <= 2 * h; ++d) {
+                    const char* rowp = rring + ((t0 + k - 2 * h + d) & 7) * 512 + l * 16;
+                    float w[4 + 2 * h];
+                    const float4 c4 = *reinterpret_cast<const float4*>(rowp);
+                    w[h] = c4.x; w[h + 1] = c4.y; w[h + 2] = c4.z; w[h + 3] = c4.w;
+                    if (h == 1) {
+                        w[0] = *reinterpret_cast<const float*>(rowp - 4);
+                        w[5] = *reinterpret_cast<const float*>(rowp + 16);
+                    } else {
+                        const float2 l2 = *reinterpret_cast<const float2*>(rowp - 8), r2 = *reinterpret_cast<const float2*>(rowp + 16);
+                        w[0] = l2.x; w[1] = l2.y; w[6] = r2.x; w[7] = r2.y;
+                    }
+                    if (d == h) { cv[0] = c4.x; cv[1] = c4.y; cv[2] = c4.z; cv[3] = c4.w; }
+#pragma unroll
+                    for (int e4 = 0; e4 < 4; ++e4)
+#pragma unroll
+                        for (int dm = -h; dm <= h; ++dm)
+                            if (!(d == h && dm == 0)) m4[e4] = fmaxf(m4[e4], w[h + e4 + dm]);
+                }
+                // strict maximum of its window (no neighbour >= centre) inside the FREAK margins; two of the four
+                // pixels of a group at most (neighbouring pixels cannot both be strict maxima)
+                const int i = o0 - h + k, j0 = xs + 4 * l;
+                unsigned long long key[2] = {0ull, 0ull};
+                int nc = 0;
+#pragma unroll
+                for (int e4 = 0; e4 < 4; ++e4) {
+                    const int j = j0 + e4;
+                    if (live && cv[e4] > m4[e4] && j >= nms_j_lo && j <= nms_j_hi) {
+                        const unsigned long long kk = ((unsigned long long)__float_as_uint(cv[e4]) << 32) | ((unsigned long long)i << 16) | (unsigned long long)j;
+                        if (nc == 0) key[0] = kk; else key[1] = kk;
+                        ++nc;
+                    }
+                }
+                const unsigned b1 = __ballot_sync(FULL, nc >= 1), b2 = __ballot_sync(FULL, nc >= 2);
+                const int n_new = __popc(b1) + __popc(b2);
+                if (n_new > 0) {  // warp-uniform: one atomic per round appends to the frame's candidate list
+                    int pos = 0;
+                    if (lane == 0) pos = atomicAdd(a.cand_count + f, n_new);
+                    pos = __shfl_sync(FULL, pos, 0) + __popc(b1 & lt) + __popc(b2 & lt);
+                    if (nc >= 1 && pos < a.cand_cap) cand[pos] = key[0];
+                    if (nc >= 2 && pos + 1 < a.cand_cap) cand[pos + 1] = key[1];
+                }
+            }
+            __syncwarp();  // the next trip overwrites ring slots and the item list read above
+        }
+    };
 
     // One trip = four steps.  STEADY trips (all four blurred / gradient / response rows inside the segment and the
     // image, a further trip to request) carry no row tests; the first four and the last one or two trips of a
@@ -302,6 +423,27 @@ k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows, int n_tas
         // (a third body specialised for interior strips was tried: 8 % SLOWER, the two steady bodies together no longer
         // fit the instruction cache; so the edge handling stays predicated on the warp-uniform edge_strip)
         const bool edge = edge_strip;
+        unsigned nz[RB] = {0u, 0u, 0u, 0u};                     // fused: lanes whose four responses of row j are not all zero
+        char* const rrow = rring + (t0 & 4) * 512 + lane * 16;  // fused: this lane's ring slots of steps t0 .. t0+3
+        if (FROM_R) {  // the response rows of this trip come from a.R (zero outside the image)
+            if (t0 >= 12) {
+#pragma unroll
+                for (int j = 0; j < RB; ++j) {
+                    const int orow = r0 + t0 + j - 6;
+                    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (orow >= 0 && orow < H && x >= 0 && x < W) {
+                        v = __ldg(reinterpret_cast<const float4*>(R + (long long)orow * R_pitch + x));
+                        if (x + 1 >= W) v.y = 0.f;
+                        if (x + 2 >= W) v.z = 0.f;
+                        if (x + 3 >= W) v.w = 0.f;
+                    }
+                    sts4(rrow + j * 512, make_uint4(__float_as_uint(v.x), __float_as_uint(v.y), __float_as_uint(v.z), __float_as_uint(v.w)));
+                    nz[j] = __ballot_sync(FULL, fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w)) > 0.f);
+                }
+                nms_trip(t0, nz);
+            }
+            return;
+        }
         // ---- 0. the four rows requested a trip ago; request the next four -----------------------------------
         uint32_t w[RB];
 #pragma unroll
@@ -437,7 +579,11 @@ k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows, int n_tas
                         shi_tomasi4(A, B, cE, cO, thr4, out);
                     }
                 }
-                if (STEADY || orow < ye) {
+                if (FUSED) {
+                    // the thresholded row goes into the ring (zeros too: slots are reused); responses are > 0 or 0
+                    sts4(rrow + j * 512, make_uint4(__float_as_uint(out[0]), __float_as_uint(out[1]), __float_as_uint(out[2]), __float_as_uint(out[3])));
+                    nz[j] = __ballot_sync(FULL, fmaxf(fmaxf(out[0], out[1]), fmaxf(out[2], out[3])) > 0.f);
+                } else if (STEADY || orow < ye) {
                     float* q = R_p + j * R_pitch;
                     asm volatile("" : "+l"(q));
                     if (st_full) stg_f4(q, out[0], out[1], out[2], out[3]);
@@ -445,6 +591,7 @@ k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows, int n_tas
                     if (st_l1) stg_f2(q + 2, out[2], out[3]);
                 }
             }
+            if (FUSED && (STEADY || t0 >= 12)) nms_trip(t0, nz);
         }
         // the ring bases swap: slot (c & 7) ^ 4 of this trip is slot c & 7 of the next
         { const char* t = qa; qa = qb; qb = t; t = ja; ja = jb; jb = t; }
@@ -491,16 +638,35 @@ int sm_count_cached() {
 
 }  // namespace
 
-cudaError_t launch_stencil(const StencilArgs& a, int n_frames, bool from_blurred, cudaStream_t st) {
-    // blurred and R rows are written with 4-byte / 16-byte vector stores at columns that are multiples of 4
-    if ((a.R_pitch & 3) || (a.R_fstride & 3) || (!from_blurred && ((a.blur_pitch & 3) || (a.blur_fstride & 3))))
+bool stencil_can_fuse(int rows, int cols, int nms_window) {
+    // fused NMS: windows 3 and 5 (half window <= 2: the ring keeps eight response rows), images with room for a candidate
+    // inside the FREAK margins (smaller images have none; they take the unfused path, whose NMS kernel launches nothing)
+    const int h = nms_window / 2;
+    if (h < 1 || h > 2) return false;
+    if (cols < 16 || rows < 8) return false;
+    const int i_lo = max(h, 35), i_hi = min(rows - h - 1, rows - 35), j_lo = max(h, 37), j_hi = min(cols - h - 1, cols - 37);
+    return i_hi >= i_lo && j_hi >= j_lo;
+}
+
+cudaError_t launch_stencil(const StencilArgs& a, int n_frames, int src, cudaStream_t st) {
+    const int nms_h = a.nms_h;
+    const bool from_blurred = src == STENCIL_SRC_BLURRED, from_R = src == STENCIL_SRC_RESPONSE;
+    if (src < 0 || src > 2 || nms_h < 0 || nms_h > 2 || (from_R && !nms_h) ||
+        (nms_h && (from_blurred || !stencil_can_fuse(a.rows, a.cols, 2 * nms_h + 1) || !a.cand || !a.cand_count)))
         return cudaErrorInvalidValue;
-    const int n_strips = (a.cols + 2 + SW - 1) / SW;  // strip s covers columns [s*SW - 2, s*SW + SW - 2)
-    // Segment height.  Every segment recomputes 12 halo rows, but the kernel is latency-bound per warp, so what
+    // blurred and R rows are written with 4-byte / 16-byte vector stores (R read with 16-byte loads) at columns that are multiples of 4
+    if (((!nms_h || from_R) && ((a.R_pitch & 3) || (a.R_fstride & 3) || (reinterpret_cast<uintptr_t>(a.R) & 15))) ||
+        (!from_blurred && !from_R && ((a.blur_pitch & 3) || (a.blur_fstride & 3))))
+        return cudaErrorInvalidValue;
+    // unfused: strip s covers columns [s*SW - 2, s*SW + SW - 2).  Fused: strip s starts at s*SWF - 4 and holds valid blurred
+    // pixels in window columns 3..124: the last strip must reach column cols-1
+    const int n_strips = nms_h ? (max(a.cols - 121, 0) + SWF - 1) / SWF + 1 : (a.cols + 2 + SW - 1) / SW;
+    // Segment height.  Every segment recomputes 12 halo rows (fused: 20), but the kernel is latency-bound per warp, so what
     // matters most is that all resident warp slots stay occupied to the end: a sweep over segment counts (KITTI at
     // batch 64/100/200, 4K at batch 1/16/64, profiles/README.md) is flat within 5 % around "three tasks per resident
-    // warp slot" and 10-25 % worse for a single under-filled wave.  Segments stay at least 48 rows high.
-    const int slots = sm_count_cached() * CTAS_PER_SM * NWARP;
+    // warp slot" and 10-25 % worse for a single under-filled wave; at 1000 KITTI frames per launch 1..4 segments are within
+    // 1 % of each other (profiles/r02a_segs.jsonl).  Segments stay at least 48 rows high.
+    const int slots = sm_count_cached() * (nms_h ? CTAS_PER_SM_FUSED : CTAS_PER_SM) * NWARP;
     const long long cols_tasks = (long long)n_strips * n_frames;
     int best_segs = (int)((3LL * slots + cols_tasks / 2) / cols_tasks);
     best_segs = max(1, min(best_segs, max(1, a.rows / 48)));
@@ -512,15 +678,24 @@ cudaError_t launch_stencil(const StencilArgs& a, int n_frames, bool from_blurred
     const dim3 grid((unsigned)((n_tasks + NWARP - 1) / NWARP));
     const bool gather = a.cols < 16 || a.rows < 8;
     const bool aligned = ((reinterpret_cast<uintptr_t>(a.in) | a.in_pitch | a.in_fstride) & 3) == 0;
-#define VO_LAUNCH(FB, GA, AL) k_stencil<FB, GA, AL><<<grid, 32 * NWARP, 0, st>>>(a, n_strips, n_segs, seg_rows, (int)n_tasks)
-    if (from_blurred) {
-        if (gather) VO_LAUNCH(true, true, false);
-        else if (aligned) VO_LAUNCH(true, false, true);
-        else VO_LAUNCH(true, false, false);
+#define VO_LAUNCH(SR, GA, AL, NH) k_stencil<SR, GA, AL, NH><<<grid, 32 * NWARP, 0, st>>>(a, n_strips, n_segs, seg_rows, (int)n_tasks)
+    if (from_R) {
+        if (nms_h == 1) VO_LAUNCH(2, false, true, 1);
+        else VO_LAUNCH(2, false, true, 2);
+    } else if (nms_h == 1) {
+        if (aligned) VO_LAUNCH(0, false, true, 1);
+        else VO_LAUNCH(0, false, false, 1);
+    } else if (nms_h == 2) {
+        if (aligned) VO_LAUNCH(0, false, true, 2);
+        else VO_LAUNCH(0, false, false, 2);
+    } else if (from_blurred) {
+        if (gather) VO_LAUNCH(1, true, false, 0);
+        else if (aligned) VO_LAUNCH(1, false, true, 0);
+        else VO_LAUNCH(1, false, false, 0);
     } else {
-        if (gather) VO_LAUNCH(false, true, false);
-        else if (aligned) VO_LAUNCH(false, false, true);
-        else VO_LAUNCH(false, false, false);
+        if (gather) VO_LAUNCH(0, true, false, 0);
+        else if (aligned) VO_LAUNCH(0, false, true, 0);
+        else VO_LAUNCH(0, false, false, 0);
     }
 #undef VO_LAUNCH
     return cudaGetLastError();

@@ -27,7 +27,7 @@ struct vo_ctx {
 
     uint8_t* d_img = nullptr;    // [total_slots][max_rows][img_pitch]  input gray
     uint8_t* d_blur = nullptr;   // same layout                         blurred gray (FREAK samples it)
-    float* d_R = nullptr;        // [total_slots][max_rows][r_pitch]    thresholded response
+    float* d_R = nullptr;        // [total_slots][max_rows][r_pitch]    thresholded response; allocated on first use (ensure_R)
     unsigned long long* d_cand = nullptr;  // [total_slots][cand_cap]   (Rbits<<32 | i<<16 | j)
     int* d_cand_count = nullptr; // [total_slots]
     float2* d_kp = nullptr;      // [total_slots][max_kp]               (x, y)
@@ -37,6 +37,9 @@ struct vo_ctx {
     int* d_flags = nullptr;      // [total_slots]  bit0: candidate overflow, bit1: bad descriptor byte
     int* slot_rows = nullptr;    // host: geometry of the frame held by each slot (0 = empty)
     int* slot_cols = nullptr;
+    float* slot_thr = nullptr;   // host: response threshold the slot was extracted with
+    bool* slot_has_R = nullptr;  // host: d_R holds the slot's response (unfused extraction / recomputed for VO_DBG_RESPONSE)
+    bool force_unfused = false;  // VO_FORCE_UNFUSED=1: extraction writes R and runs k_nms (A/B measurements, parity of both paths)
 
     // matcher scratch, per pair of a batch
     uint2* d_partial = nullptr;  // [VO_MAX_BATCH][VO_MATCH_SPLITS][max_kp]  two smallest packed keys
@@ -79,10 +82,15 @@ struct vo_ctx {
 struct StencilArgs {
     const uint8_t* in; size_t in_fstride, in_pitch;     // gray (or blurred when from_blurred)
     uint8_t* blur; size_t blur_fstride, blur_pitch;     // may be null when from_blurred
-    float* R; size_t R_fstride, R_pitch;                // floats
+    float* R; size_t R_fstride, R_pitch;                // floats; unused (may be null) when nms_h > 0
     int rows, cols; float threshold;
+    // fused non-maximum suppression: half window 1 or 2 (0 = write R instead); candidates are appended to
+    // cand[frame * cand_cap ...] with cand_count[frame] (zeroed by the caller) exactly as k_nms does
+    int nms_h; unsigned long long* cand; int cand_cap; int* cand_count;
 };
-cudaError_t launch_stencil(const StencilArgs& a, int n_frames, bool from_blurred, cudaStream_t s);
+enum { STENCIL_SRC_GRAY = 0, STENCIL_SRC_BLURRED = 1, STENCIL_SRC_RESPONSE = 2 };  // what StencilArgs::in / ::R hold on entry
+cudaError_t launch_stencil(const StencilArgs& a, int n_frames, int src, cudaStream_t s);
+bool stencil_can_fuse(int rows, int cols, int nms_window);
 cudaError_t launch_bgr2gray(const uint8_t* bgr, size_t bgr_pitch, uint8_t* gray, size_t gray_pitch, int rows, int cols,
                             cudaStream_t s);
 

@@ -48,7 +48,8 @@ extern "C" {
                                   (feature_extraction_parallel_GPU.cpp:235) */
 
 #define VO_DBG_BLURRED 1  /* rows x cols uint8, tightly packed */
-#define VO_DBG_RESPONSE 2 /* rows x cols float (thresholded R_array), tightly packed */
+#define VO_DBG_RESPONSE 2 /* rows x cols float (thresholded R_array), tightly packed; extraction keeps the response on
+                             chip (NMS fused behind the stencil), so this recomputes it from the slot's blurred image */
 #define VO_DBG_ANGLES 3   /* n float, FREAK orientation per keypoint */
 
 typedef struct vo_ctx vo_ctx;
@@ -162,6 +163,12 @@ int vo_sequence_fetch(vo_ctx* ctx, vo_seq_result* out);
 /* CUDA-event timing on the context's own compute stream. */
 int vo_timer_start(vo_ctx* ctx);
 int vo_timer_stop(vo_ctx* ctx, float* ms); /* synchronises; elapsed since vo_timer_start */
+/* The stencil kernel alone over the first `batch` frames of the uploaded sequence: mean milliseconds per launch over
+ * `reps` launches (CUDA events on the launch stream, input already in HBM, one synchronisation per launch).
+ *   mode 0  the response-writing form: u8 in -> blurred u8 + fp32 R out = 6 B/px (what vo_response / VO_DBG_RESPONSE run)
+ *   mode 1  the fused form of p->nms_window (3 or 5): u8 in -> blurred u8 out + 8 B per NMS candidate = 2 B/px
+ * The two roofline figures of bench.py come from here; they are never mixed.  Slots 0..batch-1 are overwritten. */
+int vo_bench_stencil(vo_ctx* ctx, const vo_params* p, int batch, int mode, int reps, float* ms_per_launch);
 /* Number of kernel launches issued by this context since creation (or since the last reset). */
 long long vo_launch_count(vo_ctx* ctx, int reset);
 /* Accumulated device time (ms, CUDA events) per kernel family since the last reset, when profiling is

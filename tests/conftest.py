@@ -88,3 +88,22 @@ def vo_small():
     ctx = VoFront(max_rows=480, max_cols=1241, max_keypoints=2048, n_slots=8)
     yield ctx
     ctx.close()
+
+
+@pytest.fixture(scope="session")
+def vo_small_unfused():
+    """The same context with VO_FORCE_UNFUSED=1: extraction writes the response map and runs the stand-alone k_nms
+    (the round trip the fused stencil kernel removed); both paths must give identical results."""
+    import os
+    from acs_visual_odometry_b200 import VoFront
+    old = os.environ.get("VO_FORCE_UNFUSED")
+    os.environ["VO_FORCE_UNFUSED"] = "1"          # read once, by vo_create
+    try:
+        ctx = VoFront(max_rows=480, max_cols=1241, max_keypoints=2048, n_slots=8)
+    finally:
+        if old is None:
+            del os.environ["VO_FORCE_UNFUSED"]
+        else:
+            os.environ["VO_FORCE_UNFUSED"] = old
+    yield ctx
+    ctx.close()

@@ -131,6 +131,40 @@ def test_nms_identical(vo_small, oracle, factory, kitti_pair):
     assert len(vo_small.nms(np.ones((60, 70), np.float32), 5, 10)) == 0
 
 
+def test_fused_and_unfused_nms_paths_agree(vo_small, vo_small_unfused, oracle, factory, kitti_pair):
+    """Extraction with the NMS fused behind the stencil (default: the response never leaves the SM) and with the response
+    round trip + k_nms (VO_FORCE_UNFUSED=1) both equal the oracle: windows 3 and 5 (fused), 7 and 9 (always k_nms),
+    thresholds down to 0 (every pixel a candidate group), ragged widths around the 112-column strips, and response maps
+    streamed through the fused suppression code by vo_nms."""
+    from acs_visual_odometry_b200 import Params
+    from acs_visual_odometry_b200.api import DBG_RESPONSE
+    from acs_visual_odometry_b200.synth import make_sequence
+    rng = np.random.default_rng(41)
+    imgs = [factory[0], kitti_pair[0][1], rng.integers(0, 256, (90, 131), dtype=np.uint8)]
+    imgs += [make_sequence(1, r, c, seed=50 + c, n_rects=max(40, r * c // 400))[0] for r, c in
+             ((71, 75), (80, 111), (75, 112), (96, 113), (100, 224), (77, 225), (120, 229), (83, 337), (90, 448), (72, 449))]
+    for img in imgs:
+        for p in (Params(20000.0, 3, 2000), Params(25000.0, 5, 1500), Params(0.0, 3, 2048), Params(0.0, 5, 100),
+                  Params(25000.0, 7, 300), Params(20000.0, 9, 2000)):
+            kp_o, d_o = oracle.extract(img, p.threshold, p.nms_window, p.max_keypoints)
+            for vo in (vo_small, vo_small_unfused):
+                vo.extract(img, p, slot=1)
+                kp, d, _ = vo.fetch(1, want_packed=False)
+                assert np.array_equal(kp, kp_o), (img.shape, p.threshold, p.nms_window, vo is vo_small)
+                assert len(kp) == 0 or (d == d_o).mean() >= DESC_AGREEMENT_MIN
+            # VO_DBG_RESPONSE after a fused extraction is recomputed by the writing form of the kernel: same map
+            R_f, R_u = (v.debug(1, DBG_RESPONSE, *img.shape) for v in (vo_small, vo_small_unfused))
+            assert bits_equal(R_f, R_u) and bits_equal(R_f, oracle.response(oracle.blur(img), p.threshold))
+    # response maps through both suppression codes: lattices of equal peaks, plateaus on strip borders (columns 112 k + 4)
+    R = np.zeros((150, 500), np.float32)
+    R[36:120:3, 38:460:3] = rng.uniform(1.0, 9.0, (28, 141)).astype(np.float32)
+    R[60, 114:120] = 50.0                           # plateau across the border between strips 0 and 1
+    R[70, 115] = 60.0; R[71, 116] = 60.0; R[90, 227] = 7.0; R[90, 228] = 8.0; R[91, 339] = 9.0; R[92, 340] = 9.5
+    for k, n in ((3, 2048), (5, 2048), (3, 7), (7, 2048)):
+        want = oracle.nms(R, k, n)
+        assert np.array_equal(vo_small.nms(R, k, n), want) and np.array_equal(vo_small_unfused.nms(R, k, n), want), (k, n)
+
+
 def test_describe_agreement(vo_small, oracle, factory, kitti_pair):
     worst = 1.0
     for img, tag in ((factory[0], "factory1"), (kitti_pair[0][0], "kitti")):

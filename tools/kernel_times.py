@@ -60,6 +60,13 @@ with VoFront(a.rows, a.cols, p.max_keypoints, 2 * a.batch) as vo:
     prof = vo.profile_read(reset=True)
     vo.profile_enable(False)
     nk, _, nm, _ = vo.sequence_fetch(want_kp=False, want_pairs=False)
+    # the stencil kernel alone, both forms (vo_bench_stencil): response-writing (6 B/px) and fused NMS (2 B/px)
+    nb = min(a.batch, a.frames)
+    st_unfused = vo.bench_stencil(p, nb, fused=False, reps=5)
+    try:
+        st_fused = vo.bench_stencil(p, nb, fused=True, reps=5)
+    except Exception:
+        st_fused = None
 px = a.rows * a.cols
 st_ms, st_n = prof["stencil"]
 compares = float(np.sum(nk[:-1].astype(np.float64) * nk[1:]))
@@ -69,6 +76,9 @@ out = {"tag": a.tag, "frames": a.frames, "batch": a.batch, "rows": a.rows, "cols
        "keypoints_per_frame": float(np.mean(nk)), "matches_per_pair": float(np.mean(nm)) if len(nm) else 0.0,
        "us_per_launch": {k: round(v[0] / max(v[1], 1) * 1e3, 2) for k, v in prof.items()},
        "ms_per_pass_by_kernel": {k: round(v[0] / P, 4) for k, v in prof.items()},
+       "stencil_alone_us": {"write_R_6B_per_px": round(st_unfused * 1e3, 2), "fused_nms_2B_per_px": round(st_fused * 1e3, 2) if st_fused else None,
+                            "write_R_GBps": round(6.0 * px * nb / (st_unfused / 1e3) / 1e9, 1),
+                            "fused_GBps": round(2.0 * px * nb / (st_fused / 1e3) / 1e9, 1) if st_fused else None},
        "stencil_GBps_algorithmic_6B_per_px": round(6.0 * px * a.frames * P / (st_ms / 1e3) / 1e9, 1) if st_ms else None,
        "compares_per_s_matcher_only": round(compares * P / (prof["match"][0] / 1e3), 1) if prof["match"][0] else None,
        "popc32_per_s_matcher_only": round(compares * P * (16 if a.bits == 512 else 1) / (prof["match"][0] / 1e3), 1) if prof["match"][0] else None}
