@@ -3,6 +3,7 @@
 Everything here forwards to libvofront.so; no image or descriptor arithmetic happens in Python.
 """
 import ctypes as C
+import os
 from pathlib import Path
 
 import numpy as np
@@ -16,7 +17,8 @@ _PKG = Path(__file__).resolve().parent
 
 
 def lib_path():
-    return _PKG / "libvofront.so"
+    """The in-tree library; VO_LIB names another build of the same sources (kernel tuning variants, tools/variant_bench.py)."""
+    return Path(os.environ["VO_LIB"]) if os.environ.get("VO_LIB") else _PKG / "libvofront.so"
 
 
 class VoError(RuntimeError):

@@ -9,9 +9,9 @@ import numpy as np
 _LIB = None
 _PKG = Path(__file__).resolve().parent
 
-SYMBOLS = ["vo_host_fundamental", "vo_host_sampson", "vo_host_ransac", "vo_host_get_pose", "vo_host_read_gt_line",
+SYMBOLS = ["vo_host_fundamental", "vo_host_normalize_points", "vo_host_sampson", "vo_host_ransac", "vo_host_get_pose", "vo_host_read_gt_line",
            "vo_host_format_pose_csv", "vo_host_euler", "vo_host_read_gray", "vo_host_write_png", "vo_host_write_pgm",
-           "vo_pipeline_run", "vo_host_last_error"]
+           "vo_pipeline_run", "vo_pipeline_run_ex", "vo_host_last_error"]
 
 
 class VoHostError(RuntimeError):
@@ -57,6 +57,13 @@ def fundamental(pts):
     F = np.empty(9)
     _ck(load_host_library().vo_host_fundamental(_dp(pts), len(pts), _dp(F)))
     return F.reshape(3, 3)
+
+
+def normalize_points(pts):
+    pts = _pts(pts)
+    n1, n2, T1, T2 = np.empty((len(pts), 3)), np.empty((len(pts), 3)), np.empty(9), np.empty(9)
+    _ck(load_host_library().vo_host_normalize_points(_dp(pts), len(pts), _dp(n1), _dp(n2), _dp(T1), _dp(T2)))
+    return n1, n2, T1.reshape(3, 3), T2.reshape(3, 3)
 
 
 def sampson(F, pts):
@@ -129,12 +136,14 @@ def write_pgm(path, img):
 
 
 STAT_KEYS = ["frames", "pairs_ok", "skipped_frames", "missing_frames", "rematched_pairs", "wall_s", "decode_s", "frontend_s",
-             "host_s", "compose_s", "ransac_iterations", "mean_keypoints", "mean_matches", "mean_inliers"]
+             "host_s", "compose_s", "ransac_iterations", "mean_keypoints", "mean_matches", "mean_inliers", "stale_model_pairs"]
 
 
-def pipeline_run(image_dir, num_images, pose_file, output_csv, num_threads=8, device=0, preset=1, batch=0, seed=1):
+def pipeline_run(image_dir, num_images, pose_file, output_csv, num_threads=8, device=0, preset=1, batch=0, seed=1,
+                 reuse_model=False):
     """VisualOdometry::run.  image_dir must end with a path separator, like the reference's argument."""
     stats = np.zeros(16)
-    _ck(load_host_library().vo_pipeline_run(device, num_threads, str(image_dir).encode(), num_images, str(pose_file).encode(),
-                                            str(output_csv).encode(), preset, batch, C.c_uint64(seed), _dp(stats)))
+    _ck(load_host_library().vo_pipeline_run_ex(device, num_threads, str(image_dir).encode(), num_images, str(pose_file).encode(),
+                                               str(output_csv).encode(), preset, batch, C.c_uint64(seed), int(bool(reuse_model)),
+                                               _dp(stats)))
     return dict(zip(STAT_KEYS, stats.tolist()))

@@ -44,6 +44,20 @@ int vo_host_fundamental(const double* pts, int n, double F[9]) {
     });
 }
 
+int vo_host_normalize_points(const double* pts, int n, double* n1, double* n2, double T1[9], double T2[9]) {
+    if (!pts || !n1 || !n2 || !T1 || !T2 || n < 1) return fail(-1, "null argument");
+    return guarded([&] {
+        std::vector<vo::Vec3> a, b;
+        vo::Mat3 t1, t2;
+        vo::FundamentalMatrix::normalizePoints(to_pairs(pts, n), a, b, t1, t2);
+        for (int i = 0; i < n; ++i)
+            for (int k = 0; k < 3; ++k) { n1[3 * i + k] = a[i](k); n2[3 * i + k] = b[i](k); }
+        std::memcpy(T1, t1.m, sizeof(t1.m));
+        std::memcpy(T2, t2.m, sizeof(t2.m));
+        return 0;
+    });
+}
+
 int vo_host_sampson(const double F[9], const double* pts, int n, double* err) {
     if (!F || !pts || !err || n < 0) return fail(-1, "null argument");
     const vo::Mat3 f = to_mat3(F);
@@ -137,12 +151,18 @@ int vo_host_write_pgm(const char* path, const uint8_t* gray, int rows, int cols)
 
 int vo_pipeline_run(int device, int num_threads, const char* image_dir, int num_images, const char* pose_file,
                     const char* output_csv, int preset, int batch, uint64_t seed, double* stats) {
+    return vo_pipeline_run_ex(device, num_threads, image_dir, num_images, pose_file, output_csv, preset, batch, seed, 0, stats);
+}
+
+int vo_pipeline_run_ex(int device, int num_threads, const char* image_dir, int num_images, const char* pose_file,
+                       const char* output_csv, int preset, int batch, uint64_t seed, int flags, double* stats) {
     if (!image_dir || !pose_file || !output_csv || num_images < 1 || num_threads < 1) return fail(-1, "bad argument");
     return guarded([&] {
         vo::VisualOdometry vo_("", static_cast<size_t>(num_threads), device);
         if (vo_params_preset(&vo_.params, preset) != VO_OK) return fail(-1, "unknown preset");
         if (batch > 0) vo_.batch = batch;
         vo_.seed = seed;
+        vo_.reuse_model = (flags & VO_PIPE_REUSE_MODEL) != 0;
         vo_.verbose = false;
         vo_.run(image_dir, static_cast<size_t>(num_images), pose_file, output_csv);
         const vo::RunStats& s = vo_.stats;
@@ -152,7 +172,8 @@ int vo_pipeline_run(int device, int num_threads, const char* image_dir, int num_
                                   double(s.respeculated), s.wall_s, s.decode_s, s.frontend_s, s.host_s, s.compose_s,
                                   double(s.ransac_iterations), s.mean_keypoints, s.mean_matches, s.mean_inliers};
             std::memcpy(stats, v, sizeof(v));
-            stats[14] = stats[15] = 0;
+            stats[14] = double(s.stale_model_pairs);
+            stats[15] = 0;
         }
         return 0;
     });

@@ -42,6 +42,8 @@ struct VisualOdometry::PairResult {
     Mat3 R = Mat3::identity();
     Vec3 t{{0, 0, 0}};  // unit length; scaled with the ground-truth step in the composition stage
     int n_matches = 0, n_inliers = 0, iterations = 0;
+    Mat3 F = Mat3::zero();           // the fitted model of an OK pair (what the reference's long-lived model would hold)
+    std::vector<PointPair> inliers;
 };
 
 VisualOdometry::VisualOdometry(const std::string&, std::size_t num_threads, int device)
@@ -139,6 +141,7 @@ void VisualOdometry::solve_pair(const float* kp1, const float* kp2, const int32_
         const PoseResult pr = estimator.getPoseEx(model.getMatrix(), p1, p2, 1.0);
         out.R = pr.R; out.t = pr.t;
         out.status = PairResult::OK;
+        if (reuse_model) { out.F = model.getMatrix(); out.inliers = inl; }
     } catch (const std::runtime_error&) {
         out.status = PairResult::DEGENERATE;  // the reference would terminate on the uncaught exception
     }
@@ -258,6 +261,8 @@ void VisualOdometry::run(const std::string image_dir, const size_t num_images, c
 
     // ---- stage 4: sequential composition with the reference's skip rules
     size_t last_valid = 0;
+    Mat3 model_F = Mat3::zero();               // reuse_model: the state of the reference's long-lived model
+    std::vector<PointPair> model_inliers;
     double sum_kp = 0, sum_m = 0, sum_inl = 0;
     size_t n_kp = 0, n_m = 0;
     bool warned_gt = false;
@@ -293,6 +298,23 @@ void VisualOdometry::run(const std::string image_dir, const size_t num_images, c
             }
             stats.ransac_iterations += r.iterations;
             sum_m += r.n_matches; ++n_m;
+            if (reuse_model) {
+                if (r.status == PairResult::OK) {
+                    model_F = r.F; model_inliers = r.inliers;
+                } else if (r.status == PairResult::FEW_INLIERS && model_inliers.size() >= 8) {
+                    // the reference's model object still holds the previous pair's fit: pose from that (see vo_pipeline.hpp)
+                    std::vector<Point2f> p1(model_inliers.size()), p2(model_inliers.size());
+                    for (size_t q = 0; q < model_inliers.size(); ++q) {
+                        p1[q] = Point2f{static_cast<float>(model_inliers[q].first.x), static_cast<float>(model_inliers[q].first.y)};
+                        p2[q] = Point2f{static_cast<float>(model_inliers[q].second.x), static_cast<float>(model_inliers[q].second.y)};
+                    }
+                    PoseUpdate estimator;
+                    const PoseResult pr = estimator.getPoseEx(model_F, p1, p2, 1.0);
+                    r.R = pr.R; r.t = pr.t; r.n_inliers = static_cast<int>(model_inliers.size());
+                    r.status = PairResult::OK;
+                    ++stats.stale_model_pairs;
+                }
+            }
             if (r.status != PairResult::OK) {
                 if (r.status == PairResult::FEW_MATCHES && verbose) std::fprintf(stderr, "Too few matches at frame %zu\n", i);
                 if (anchor_id != last_valid) {  // keep the query frame's pixels for the pairs to come

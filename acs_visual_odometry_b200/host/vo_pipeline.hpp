@@ -32,6 +32,7 @@ struct KeyPoint {  // the fields of cv::KeyPoint the pipeline uses
 
 struct RunStats {
     size_t frames = 0, pairs_ok = 0, skipped_frames = 0, missing_frames = 0, respeculated = 0;
+    size_t stale_model_pairs = 0;  // reuse_model only: pairs whose pose came from the previous pair's model
     double wall_s = 0;        // whole run
     double decode_s = 0;      // sum over chunks, overlapped with the rest
     double frontend_s = 0;    // sum of vo_sequence_run calls (H2D + kernels + D2H)
@@ -59,6 +60,12 @@ public:
     int batch = 64;              // frames per chunk
     std::uint64_t seed = 0;      // 0: std::random_device per pair, like the reference; else pair i uses seed + i
     double ransac_probability = 0.99, sampson_threshold = 1.0;  // VisualOdometry.cpp:125
+    // The reference keeps ONE FundamentalMatrix across frames (VisualOdometry.cpp:49); when a RANSAC run ends without a
+    // consensus set of 8, FundamentalMatrix::fit returns early (ransac.cpp:95-96) and the frame is processed with the
+    // PREVIOUS pair's F and inliers instead of being skipped.  true restates that; false (default) fits a fresh model
+    // per pair, so the "< 8 inliers" guard (VisualOdometry.cpp:147) skips the frame.  Both are checked against the
+    // sequential restatement oracle/vo_loop_oracle.py (tests/test_gpu_pipeline.py).
+    bool reuse_model = false;
     bool verbose = true;
     RunStats stats;
     const std::vector<Mat4>& poses() const { return estimated_poses_; }

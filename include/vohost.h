@@ -19,6 +19,8 @@ extern "C" {
 
 /* FundamentalMatrix::computeFundamentalMatrix (ransac.cpp:63-93): normalised 8-point fit, rank 2 enforced. n >= 8. */
 int vo_host_fundamental(const double* pts, int n, double F[9]);
+/* FundamentalMatrix::normalizePoints (ransac.cpp:25-61): n1, n2 receive n x 3 normalised homogeneous points. */
+int vo_host_normalize_points(const double* pts, int n, double* n1, double* n2, double T1[9], double T2[9]);
 /* computeSampsonError (ransac.cpp:12-23) for n correspondences. */
 int vo_host_sampson(const double F[9], const double* pts, int n, double* err);
 /* Ransac::run (ransac.cpp:120-194).  seed 0 = std::random_device like the reference.  inliers (may be NULL)
@@ -48,6 +50,12 @@ int vo_host_write_pgm(const char* path, const uint8_t* gray, int rows, int cols)
  * 12 mean matches, 13 mean inliers. */
 int vo_pipeline_run(int device, int num_threads, const char* image_dir, int num_images, const char* pose_file,
                     const char* output_csv, int preset, int batch, uint64_t seed, double* stats);
+/* The same with flags: VO_PIPE_REUSE_MODEL keeps one FundamentalMatrix across frames like the reference does
+ * (VisualOdometry.cpp:49): a pair whose RANSAC run ends without a consensus set of 8 is then processed with the
+ * previous pair's F and inliers (ransac.cpp:95-96 returns early) instead of being skipped.  stats[14] counts them. */
+#define VO_PIPE_REUSE_MODEL 1
+int vo_pipeline_run_ex(int device, int num_threads, const char* image_dir, int num_images, const char* pose_file,
+                       const char* output_csv, int preset, int batch, uint64_t seed, int flags, double* stats);
 /* message of the last failure on this thread */
 const char* vo_host_last_error(void);
 
