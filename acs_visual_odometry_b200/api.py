@@ -98,6 +98,7 @@ def load_library():
         "vo_timer_start": (i, [vp]),
         "vo_timer_stop": (i, [vp, P(f)]),
         "vo_bench_stencil": (i, [vp, P(_CParams), i, i, i, P(f)]),
+        "vo_bench_popc": (i, [vp, i, i, P(C.c_double)]),
         "vo_launch_count": (C.c_longlong, [vp, i]),
         "vo_profile_enable": (i, [vp, i]),
         "vo_profile_read": (i, [vp, P(f), P(C.c_longlong), i]),
@@ -321,6 +322,12 @@ class VoFront:
         ms = C.c_float()
         self._ck(self.lib.vo_bench_stencil(self.h, C.byref(params.c()), batch, int(bool(fused)), reps, C.byref(ms)))
         return ms.value
+
+    def bench_popc(self, mode=0, reps=5):
+        """POPC32 per second of this GPU (see vofront.h)."""
+        v = C.c_double()
+        self._ck(self.lib.vo_bench_popc(self.h, mode, reps, C.byref(v)))
+        return v.value
 
     def launch_count(self, reset=False):
         return self.lib.vo_launch_count(self.h, int(reset))

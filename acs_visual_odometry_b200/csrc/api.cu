@@ -6,6 +6,8 @@
 #include <cstdlib>
 #include <cstring>
 
+#include <algorithm>
+
 #include "vo_internal.cuh"
 
 namespace {
@@ -845,6 +847,30 @@ int vo_bench_stencil(vo_ctx* c, const vo_params* p, int batch, int mode, int rep
     }
     for (int k = 0; k < batch; ++k) { c->slot_rows[k] = 0; c->slot_has_R[k] = false; }  // the slots hold no complete frame record
     *ms_per_launch = total / reps;
+    return VO_OK;
+}
+
+int vo_bench_popc(vo_ctx* c, int mode, int reps, double* popc32_per_s) {
+    if (!c) return VO_ERR_BAD_ARG;
+    if (!popc32_per_s || reps < 1 || (mode != 0 && mode != 1)) return fail(c, VO_ERR_BAD_ARG, "bad arguments");
+    CK(c, cudaSetDevice(c->device));
+    int sms = 0;
+    CK(c, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device));
+    unsigned* scratch = reinterpret_cast<unsigned*>(c->d_cand_count);  // one word that is never written in practice
+    double best = 0.0;
+    for (int r = 0; r < reps + 1; ++r) {  // first launch is the warm-up
+        double n = 0;
+        CK(c, cudaEventRecord(c->ev_t0, c->s_compute));
+        cudaError_t e = launch_popc_peak(mode, scratch, sms, 4096, c->s_compute, &n);
+        c->launches++;
+        if (e != cudaSuccess) return fail_cuda(c, e, "launch_popc_peak");
+        CK(c, cudaEventRecord(c->ev_t1, c->s_compute));
+        CK(c, cudaEventSynchronize(c->ev_t1));
+        float ms = 0.f;
+        CK(c, cudaEventElapsedTime(&ms, c->ev_t0, c->ev_t1));
+        if (r > 0 && ms > 0.f) best = std::max(best, n / (ms * 1e-3));
+    }
+    *popc32_per_s = best;
     return VO_OK;
 }
 

@@ -173,7 +173,35 @@ __global__ void __launch_bounds__(FN_NT) k_finalize(const MatchArgs a) {
     if (tid == 0) a.nmatch[pair] = s_base;
 }
 
+// POPC32 issue rate of this GPU: the denominator of the matcher's roofline.  Every thread runs
+// eight independent chains.  WITH_XOR_ADD = the matcher's own instruction mix per compare (XOR, POPC, two adds).
+template <bool WITH_XOR_ADD>
+__global__ void k_popc_peak(unsigned* out, unsigned seed, int iters) {
+    unsigned a[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) a[i] = seed * (threadIdx.x + 1) + i * 0x9E3779B9u + blockIdx.x;
+    unsigned acc = 0;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            if (WITH_XOR_ADD) { acc += __popc(a[i] ^ acc); a[i] += 0x01010101u; }
+            else a[i] = __popc(a[i]) + a[i];
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc += a[i];
+    if (acc == 0x12345678u) out[0] = acc;  // never true in practice: keeps the chains alive
+}
+
 }  // namespace
+
+cudaError_t launch_popc_peak(int mode, unsigned* scratch, int sms, int iters, cudaStream_t st, double* popc_per_launch) {
+    const int threads = 256, blocks = sms * 8;
+    if (mode == 0) k_popc_peak<false><<<blocks, threads, 0, st>>>(scratch, 12345u, iters);
+    else k_popc_peak<true><<<blocks, threads, 0, st>>>(scratch, 12345u, iters);
+    *popc_per_launch = (double)blocks * threads * iters * 8;
+    return cudaGetLastError();
+}
 
 cudaError_t launch_match(const MatchArgs& a, int n_pairs, int max_n1, cudaStream_t st) {
     if (n_pairs <= 0 || max_n1 <= 0) return cudaSuccess;

@@ -125,6 +125,7 @@ struct MatchArgs {
 };
 cudaError_t launch_match(const MatchArgs& a, int n_pairs, int max_n1, cudaStream_t s_);
 cudaError_t launch_match_finalize(const MatchArgs& a, int n_pairs, cudaStream_t s);
+cudaError_t launch_popc_peak(int mode, unsigned* scratch, int sms, int iters, cudaStream_t st, double* popc_per_launch);
 
 cudaError_t launch_pack_bytes(const uint8_t* bytes, int n, uint32_t* packed, int* flag, cudaStream_t s);
 cudaError_t launch_unpack_bytes(const uint32_t* packed, int n, uint8_t* bytes, cudaStream_t s);
