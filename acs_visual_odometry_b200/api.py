@@ -99,6 +99,7 @@ def load_library():
         "vo_timer_stop": (i, [vp, P(f)]),
         "vo_bench_stencil": (i, [vp, P(_CParams), i, i, i, P(f)]),
         "vo_bench_popc": (i, [vp, i, i, P(C.c_double)]),
+        "vo_bench_candidates": (i, [vp, i, P(C.c_longlong)]),
         "vo_launch_count": (C.c_longlong, [vp, i]),
         "vo_profile_enable": (i, [vp, i]),
         "vo_profile_read": (i, [vp, P(f), P(C.c_longlong), i]),
@@ -322,6 +323,12 @@ class VoFront:
         ms = C.c_float()
         self._ck(self.lib.vo_bench_stencil(self.h, C.byref(params.c()), batch, int(bool(fused)), reps, C.byref(ms)))
         return ms.value
+
+    def bench_candidates(self, batch):
+        """Candidates appended by the last fused stencil launch over its first `batch` frames (see vofront.h)."""
+        v = C.c_longlong()
+        self._ck(self.lib.vo_bench_candidates(self.h, batch, C.byref(v)))
+        return v.value
 
     def bench_popc(self, mode=0, reps=5):
         """POPC32 per second of this GPU (see vofront.h)."""

@@ -850,6 +850,19 @@ int vo_bench_stencil(vo_ctx* c, const vo_params* p, int batch, int mode, int rep
     return VO_OK;
 }
 
+int vo_bench_candidates(vo_ctx* c, int batch, long long* total) {
+    if (!c) return VO_ERR_BAD_ARG;
+    if (!total || batch < 1 || batch > c->n_slots || batch > VO_MAX_BATCH) return fail(c, VO_ERR_BAD_ARG, "bad arguments");
+    CK(c, cudaSetDevice(c->device));
+    std::vector<int> h(batch);
+    CK(c, cudaMemcpyAsync(h.data(), c->d_cand_count, sizeof(int) * batch, cudaMemcpyDeviceToHost, c->s_compute));
+    CK(c, cudaStreamSynchronize(c->s_compute));
+    long long sum = 0;
+    for (int v : h) sum += v;
+    *total = sum;
+    return VO_OK;
+}
+
 int vo_bench_popc(vo_ctx* c, int mode, int reps, double* popc32_per_s) {
     if (!c) return VO_ERR_BAD_ARG;
     if (!popc32_per_s || reps < 1 || (mode != 0 && mode != 1)) return fail(c, VO_ERR_BAD_ARG, "bad arguments");

@@ -169,6 +169,9 @@ int vo_timer_stop(vo_ctx* ctx, float* ms); /* synchronises; elapsed since vo_tim
  *   mode 1  the fused form of p->nms_window (3 or 5): u8 in -> blurred u8 out + 8 B per NMS candidate = 2 B/px
  * The two roofline figures of bench.py come from here; they are never mixed.  Slots 0..batch-1 are overwritten. */
 int vo_bench_stencil(vo_ctx* ctx, const vo_params* p, int batch, int mode, int reps, float* ms_per_launch);
+/* Sum over the first `batch` frames of the candidate counts the last fused stencil launch appended (the 8 B per
+ * candidate term of the fused kernel's algorithmic bytes).  Call right after vo_bench_stencil(mode 1). */
+int vo_bench_candidates(vo_ctx* ctx, int batch, long long* total);
 /* The POPC32 issue rate of this GPU, measured by a small kernel of independent chains on the context's stream (best of
  * `reps` launches, CUDA events): the denominator of the matcher's roofline (16 POPC32 per 512-bit compare, 1 in REF32
  * mode).  mode 0: POPC + one add per chain step; mode 1: the matcher's own mix per compare (XOR, POPC, two adds). */
