@@ -10,6 +10,7 @@ import numpy as np
 
 MATCH_REF32 = 32
 MATCH_FULL512 = 512
+RESPONSE_SHI_TOMASI, RESPONSE_HARRIS = 0, 1
 DBG_BLURRED, DBG_RESPONSE, DBG_ANGLES = 1, 2, 3
 _ERR = {-1: "VO_ERR_BAD_ARG", -2: "VO_ERR_CUDA", -3: "VO_ERR_CAPACITY", -4: "VO_ERR_NO_DEVICE", -5: "VO_ERR_STATE"}
 
@@ -29,7 +30,7 @@ class VoError(RuntimeError):
 
 class _CParams(C.Structure):
     _fields_ = [("threshold", C.c_float), ("nms_window", C.c_int), ("max_keypoints", C.c_int), ("ratio", C.c_float),
-                ("match_bits", C.c_int)]
+                ("match_bits", C.c_int), ("response", C.c_int), ("harris_k", C.c_float)]
 
 
 class _CSeqResult(C.Structure):
@@ -39,9 +40,11 @@ class _CSeqResult(C.Structure):
 class Params:
     """vo_params: the literals the reference scatters over globals and call sites."""
 
-    def __init__(self, threshold=25000.0, nms_window=5, max_keypoints=1500, ratio=0.75, match_bits=MATCH_REF32):
+    def __init__(self, threshold=25000.0, nms_window=5, max_keypoints=1500, ratio=0.75, match_bits=MATCH_REF32,
+                 response=RESPONSE_SHI_TOMASI, harris_k=0.04):
         self.threshold, self.nms_window, self.max_keypoints = float(threshold), int(nms_window), int(max_keypoints)
         self.ratio, self.match_bits = float(ratio), int(match_bits)
+        self.response, self.harris_k = int(response), float(harris_k)
 
     @classmethod
     def cpu_ref(cls, **kw):  # corner_detection_parallel.h:16, feature_extraction_parallel.cpp:274
@@ -52,7 +55,7 @@ class Params:
         return cls(20000.0, 3, 2000, **kw)
 
     def c(self):
-        return _CParams(self.threshold, self.nms_window, self.max_keypoints, self.ratio, self.match_bits)
+        return _CParams(self.threshold, self.nms_window, self.max_keypoints, self.ratio, self.match_bits, self.response, self.harris_k)
 
 
 _lib = None
@@ -86,6 +89,10 @@ def load_library():
         "vo_debug_fetch": (i, [vp, i, i, vp]),
         "vo_blur": (i, [vp, vp, i, i, vp]),
         "vo_response": (i, [vp, vp, i, i, f, vp]),
+        "vo_response_p": (i, [vp, vp, i, i, P(_CParams), vp]),
+        "vo_bgr2gray": (i, [vp, vp, i, i, sz, vp]),
+        "vo_gradients": (i, [vp, vp, i, i, sz, i, i, i, i, vp, vp, vp]),
+        "vo_response_from_gradients": (i, [vp, vp, vp, vp, i, i, i, i, i, i, P(_CParams), vp]),
         "vo_nms": (i, [vp, vp, i, i, i, i, vp, P(i)]),
         "vo_describe": (i, [vp, vp, i, i, vp, i, vp, vp]),
         "vo_match": (i, [vp, i, i, f, i, vp, i, P(i)]),
@@ -222,6 +229,37 @@ class VoFront:
         out = np.empty(blurred.shape, np.float32)
         self._ck(self.lib.vo_response(self.h, _ptr(blurred), blurred.shape[0], blurred.shape[1], threshold, _ptr(out)))
         return out
+
+    def response_p(self, blurred, params):
+        blurred = np.ascontiguousarray(blurred, np.uint8)
+        out = np.empty(blurred.shape, np.float32)
+        self._ck(self.lib.vo_response_p(self.h, _ptr(blurred), blurred.shape[0], blurred.shape[1], C.byref(params.c()), _ptr(out)))
+        return out
+
+    def bgr2gray(self, bgr):
+        bgr = np.ascontiguousarray(bgr, np.uint8)
+        out = np.empty(bgr.shape[:2], np.uint8)
+        self._ck(self.lib.vo_bgr2gray(self.h, _ptr(bgr), bgr.shape[0], bgr.shape[1], bgr.strides[0], _ptr(out)))
+        return out
+
+    def gradients(self, picture, interval=None, out=None):
+        """direction_gradients_worker over interval = (r0, r1, c0, c1) (default: the whole image); `out` = (Jx, Jy, Jxy) to
+        write into (zero matrices by default, like the manager's cv::Mat::zeros)."""
+        picture = np.ascontiguousarray(picture, np.uint8)
+        rows, cols = picture.shape
+        r0, r1, c0, c1 = interval or (0, rows, 0, cols)
+        jx, jy, jxy = out if out is not None else (np.zeros((rows, cols), np.float32) for _ in range(3))
+        self._ck(self.lib.vo_gradients(self.h, _ptr(picture), rows, cols, picture.strides[0], r0, r1, c0, c1, _ptr(jx), _ptr(jy), _ptr(jxy)))
+        return jx, jy, jxy
+
+    def response_from_gradients(self, jx, jy, jxy, params, interval=None, out=None):
+        jx, jy, jxy = (np.ascontiguousarray(a, np.float32) for a in (jx, jy, jxy))
+        rows, cols = jx.shape
+        r0, r1, c0, c1 = interval or (0, rows, 0, cols)
+        R = out if out is not None else np.zeros((rows, cols), np.float32)
+        self._ck(self.lib.vo_response_from_gradients(self.h, _ptr(jx), _ptr(jy), _ptr(jxy), rows, cols, r0, r1, c0, c1,
+                                                     C.byref(params.c()), _ptr(R)))
+        return R
 
     def nms(self, R, nms_window=5, max_keypoints=1500):
         R = np.ascontiguousarray(R, np.float32)

@@ -56,6 +56,10 @@ int check_params(vo_ctx* c, const vo_params* p) {
     if (p->match_bits != VO_MATCH_REF32 && p->match_bits != VO_MATCH_FULL512)
         return fail(c, VO_ERR_BAD_ARG, "match_bits must be 32 or 512");
     if (!(p->threshold >= 0.0f)) return fail(c, VO_ERR_BAD_ARG, "threshold must be >= 0");
+    if (p->response != VO_RESPONSE_SHI_TOMASI && p->response != VO_RESPONSE_HARRIS)
+        return fail(c, VO_ERR_BAD_ARG, "response must be VO_RESPONSE_SHI_TOMASI or VO_RESPONSE_HARRIS");
+    if (p->response == VO_RESPONSE_HARRIS && !(p->harris_k >= 0.0f && p->harris_k <= 1.0f))
+        return fail(c, VO_ERR_BAD_ARG, "harris_k must be in [0, 1]");
     return VO_OK;
 }
 int check_geom(vo_ctx* c, int rows, int cols, size_t pitch, size_t min_pitch) {
@@ -82,7 +86,8 @@ int run_extract(vo_ctx* c, const uint8_t* in_base, size_t in_fstride, size_t in_
     CK(c, cudaMemsetAsync(c->d_cand_count + so, 0, sizeof(int) * n, c->s_cur));
     CK(c, cudaMemsetAsync(c->d_flags + so, 0, sizeof(int) * n, c->s_cur));
     // Fused path: the stencil kernel keeps the response on chip and appends the NMS candidates itself (no R round trip).
-    const bool fused = !from_blurred && !stop_after_response && !c->force_unfused && stencil_can_fuse(rows, cols, p->nms_window);
+    const bool fused = !from_blurred && !stop_after_response && !c->force_unfused && p->response == VO_RESPONSE_SHI_TOMASI &&
+                       stencil_can_fuse(rows, cols, p->nms_window);
     int rc_;
     if (!fused && (rc_ = ensure_R(c))) return rc_;
     StencilArgs sa;
@@ -90,6 +95,7 @@ int run_extract(vo_ctx* c, const uint8_t* in_base, size_t in_fstride, size_t in_
     sa.blur = c->d_blur + so * c->img_fstride; sa.blur_fstride = c->img_fstride; sa.blur_pitch = c->img_pitch;
     sa.R = fused ? nullptr : c->d_R + so * c->r_fstride; sa.R_fstride = c->r_fstride; sa.R_pitch = c->r_pitch;
     sa.rows = rows; sa.cols = cols; sa.threshold = p->threshold;
+    sa.response = p->response; sa.harris_k = p->harris_k;
     sa.nms_h = fused ? p->nms_window / 2 : 0;
     sa.cand = c->d_cand + so * c->cand_cap; sa.cand_cap = c->cand_cap; sa.cand_count = c->d_cand_count + so;
     RUN(c, FAM_STENCIL, launch_stencil(sa, n, from_blurred ? STENCIL_SRC_BLURRED : STENCIL_SRC_GRAY, c->s_cur));
@@ -210,6 +216,8 @@ int vo_params_preset(vo_params* p, int preset) {
     if (!p) return VO_ERR_BAD_ARG;
     p->ratio = 0.75f;
     p->match_bits = VO_MATCH_REF32;
+    p->response = VO_RESPONSE_SHI_TOMASI;
+    p->harris_k = 0.04f;  // the usual Harris constant; read only when response == VO_RESPONSE_HARRIS
     if (preset == VO_PRESET_CPU_REF) { p->threshold = 25000.0f; p->nms_window = 5; p->max_keypoints = 1500; }
     else if (preset == VO_PRESET_VO_GPU_REF) { p->threshold = 20000.0f; p->nms_window = 3; p->max_keypoints = 2000; }
     else return VO_ERR_BAD_ARG;
@@ -482,18 +490,102 @@ int vo_blur(vo_ctx* c, const uint8_t* gray, int rows, int cols, uint8_t* blurred
 }
 
 int vo_response(vo_ctx* c, const uint8_t* blurred, int rows, int cols, float threshold, float* R) {
+    vo_params p; vo_params_preset(&p, VO_PRESET_CPU_REF); p.threshold = threshold;
+    return vo_response_p(c, blurred, rows, cols, &p, R);
+}
+
+int vo_response_p(vo_ctx* c, const uint8_t* blurred, int rows, int cols, const vo_params* pp, float* R) {
     if (!c) return VO_ERR_BAD_ARG;
-    if (!blurred || !R) return fail(c, VO_ERR_BAD_ARG, "NULL buffer");
+    if (!blurred || !R || !pp) return fail(c, VO_ERR_BAD_ARG, "NULL buffer");
     int rc;
     if ((rc = check_geom(c, rows, cols, (size_t)cols, (size_t)cols))) return rc;
-    if (!(threshold >= 0.0f)) return fail(c, VO_ERR_BAD_ARG, "threshold must be >= 0");
+    vo_params p = *pp; p.max_keypoints = 1; p.nms_window = 5; p.match_bits = VO_MATCH_REF32;
+    if ((rc = check_params(c, &p))) return rc;
     CK(c, cudaSetDevice(c->device));
     const int slot = c->n_slots;
     uint8_t* dst = c->d_img + (size_t)slot * c->img_fstride;
     CK(c, cudaMemcpy2DAsync(dst, c->img_pitch, blurred, (size_t)cols, (size_t)cols, (size_t)rows, cudaMemcpyHostToDevice, c->s_compute));
-    vo_params p; vo_params_preset(&p, VO_PRESET_CPU_REF); p.max_keypoints = 1; p.threshold = threshold;
     if ((rc = run_extract(c, dst, c->img_fstride, c->img_pitch, 1, rows, cols, &p, slot, true, true))) return rc;
     return vo_debug_fetch(c, slot, VO_DBG_RESPONSE, R);
+}
+
+// ---- per-stage workers with the reference's interval semantics (façade classes of vofront_adapter.hpp) --------------
+namespace {
+struct DevBuf {  // stage calls are not on the hot path: they allocate what they need and free it on return
+    void* p = nullptr;
+    ~DevBuf() { if (p) cudaFree(p); }
+};
+bool interval_ok(int rows, int cols, int r0, int r1, int c0, int c1) {
+    return r0 >= 0 && c0 >= 0 && r1 <= rows && c1 <= cols && r0 <= r1 && c0 <= c1;
+}
+}  // namespace
+
+int vo_bgr2gray(vo_ctx* c, const uint8_t* bgr, int rows, int cols, size_t pitch, uint8_t* gray) {
+    if (!c) return VO_ERR_BAD_ARG;
+    if (!bgr || !gray) return fail(c, VO_ERR_BAD_ARG, "NULL buffer");
+    int rc;
+    if ((rc = check_geom(c, rows, cols, pitch, (size_t)cols * 3))) return rc;
+    CK(c, cudaSetDevice(c->device));
+    CK(c, cudaMemcpy2DAsync(c->d_bytes, (size_t)cols * 3, bgr, pitch, (size_t)cols * 3, (size_t)rows, cudaMemcpyHostToDevice, c->s_compute));
+    uint8_t* dst = c->d_img + (size_t)c->n_slots * c->img_fstride;
+    RUN(c, FAM_MISC, launch_bgr2gray(c->d_bytes, (size_t)cols * 3, dst, c->img_pitch, rows, cols, c->s_compute));
+    CK(c, cudaMemcpy2DAsync(gray, (size_t)cols, dst, c->img_pitch, (size_t)cols, (size_t)rows, cudaMemcpyDeviceToHost, c->s_compute));
+    CK(c, cudaStreamSynchronize(c->s_compute));
+    return VO_OK;
+}
+
+int vo_gradients(vo_ctx* c, const uint8_t* picture, int rows, int cols, size_t pitch, int r0, int r1, int c0, int c1, float* Jx, float* Jy,
+                 float* Jxy) {
+    if (!c) return VO_ERR_BAD_ARG;
+    if (!picture || !Jx || !Jy || !Jxy) return fail(c, VO_ERR_BAD_ARG, "NULL buffer");
+    int rc;
+    if ((rc = check_geom(c, rows, cols, pitch, (size_t)cols))) return rc;
+    if (!interval_ok(rows, cols, r0, r1, c0, c1)) return fail(c, VO_ERR_BAD_ARG, "interval outside the image");
+    const int w = c1 - c0 - 2, h = r1 - r0 - 2;
+    if (w <= 0 || h <= 0) return VO_OK;  // the reference's loops run zero times
+    CK(c, cudaSetDevice(c->device));
+    uint8_t* dimg = c->d_img + (size_t)c->n_slots * c->img_fstride;
+    CK(c, cudaMemcpy2DAsync(dimg, c->img_pitch, picture, pitch, (size_t)cols, (size_t)rows, cudaMemcpyHostToDevice, c->s_compute));
+    DevBuf g;
+    const size_t plane = (size_t)rows * cols;
+    CK(c, cudaMalloc(&g.p, 3 * plane * sizeof(float)));
+    float* d = static_cast<float*>(g.p);
+    RUN(c, FAM_MISC, launch_gradients_ref(dimg, c->img_pitch, r0, r1, c0, c1, d, d + plane, d + 2 * plane, cols, c->s_compute));
+    // only the rectangle the worker writes goes back: the rest of the caller's matrices stays as it is
+    float* dst[3] = {Jx, Jy, Jxy};
+    const size_t off = (size_t)(r0 + 1) * cols + (c0 + 1);
+    for (int k = 0; k < 3; ++k)
+        CK(c, cudaMemcpy2DAsync(dst[k] + off, (size_t)cols * 4, d + k * plane + off, (size_t)cols * 4, (size_t)w * 4, (size_t)h,
+                                cudaMemcpyDeviceToHost, c->s_compute));
+    CK(c, cudaStreamSynchronize(c->s_compute));
+    return VO_OK;
+}
+
+int vo_response_from_gradients(vo_ctx* c, const float* Jx, const float* Jy, const float* Jxy, int rows, int cols, int r0, int r1, int c0,
+                               int c1, const vo_params* pp, float* R) {
+    if (!c) return VO_ERR_BAD_ARG;
+    if (!Jx || !Jy || !Jxy || !R || !pp) return fail(c, VO_ERR_BAD_ARG, "NULL buffer");
+    if (rows < 1 || cols < 1) return fail(c, VO_ERR_BAD_ARG, "empty image");
+    vo_params p = *pp; p.max_keypoints = 1; p.nms_window = 5; p.match_bits = VO_MATCH_REF32;
+    int rc;
+    if ((rc = check_params(c, &p))) return rc;
+    if (!interval_ok(rows, cols, r0, r1, c0, c1)) return fail(c, VO_ERR_BAD_ARG, "interval outside the image");
+    const int w = c1 - c0 - 4, h = r1 - r0 - 4;
+    if (w <= 0 || h <= 0) return VO_OK;
+    CK(c, cudaSetDevice(c->device));
+    DevBuf g;
+    const size_t plane = (size_t)rows * cols;
+    CK(c, cudaMalloc(&g.p, 4 * plane * sizeof(float)));
+    float* d = static_cast<float*>(g.p);
+    const float* src[3] = {Jx, Jy, Jxy};
+    for (int k = 0; k < 3; ++k) CK(c, cudaMemcpyAsync(d + k * plane, src[k], plane * sizeof(float), cudaMemcpyHostToDevice, c->s_compute));
+    RUN(c, FAM_MISC, launch_response_ref(d, d + plane, d + 2 * plane, cols, r0, r1, c0, c1, p.threshold, p.response, p.harris_k, d + 3 * plane,
+                                         c->s_compute));
+    const size_t off = (size_t)(r0 + 2) * cols + (c0 + 2);
+    CK(c, cudaMemcpy2DAsync(R + off, (size_t)cols * 4, d + 3 * plane + off, (size_t)cols * 4, (size_t)w * 4, (size_t)h, cudaMemcpyDeviceToHost,
+                            c->s_compute));
+    CK(c, cudaStreamSynchronize(c->s_compute));
+    return VO_OK;
 }
 
 int vo_nms(vo_ctx* c, const float* R, int rows, int cols, int nms_window, int max_keypoints, float* kp_xy, int* n_out) {

@@ -123,20 +123,46 @@ __global__ void __launch_bounds__(SEL_NT) k_select(const SelectArgs a) {
             if (tid < 256) s_hist[tid] = 0;
             __syncthreads();
             const unsigned long long prefix = s_prefix;
-            for (int q = tid; q < M; q += SEL_NT) {
-                const unsigned long long key = cand[q];
-                const bool in = (shift == 56) || ((key >> (shift + 8)) == (prefix >> (shift + 8)));
-                if (in) atomicAdd(&s_hist[(int)((key >> shift) & 255ull)], 1);
+            // four keys in flight per thread: the sweep is a chain of L2 round trips otherwise
+            for (int q0 = tid; q0 < M; q0 += 4 * SEL_NT) {
+                unsigned long long key[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) key[u] = q0 + u * SEL_NT < M ? cand[q0 + u * SEL_NT] : 0ull;
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const bool in = q0 + u * SEL_NT < M && ((shift == 56) || ((key[u] >> (shift + 8)) == (prefix >> (shift + 8))));
+                    if (in) atomicAdd(&s_hist[(int)((key[u] >> shift) & 255ull)], 1);
+                }
             }
             __syncthreads();
-            if (tid == 0) {
-                int rem = s_remaining, d = 255;
-                for (; d > 0; --d) {
-                    if (s_hist[d] >= rem) break;
-                    rem -= s_hist[d];
+            if (tid < 32) {
+                // the digit holding the rem-th largest key: walk the histogram from the top.  Lane l owns bins 8l .. 8l+7;
+                // a suffix scan over the lanes finds the owner, which walks its own eight bins (a single thread walking
+                // all 256 bins eight times over was a third of the kernel at 8000 keypoints per frame)
+                int h8[8], own = 0;
+#pragma unroll
+                for (int b = 0; b < 8; ++b) { h8[b] = s_hist[8 * tid + b]; own += h8[b]; }
+                int incl = own;
+#pragma unroll
+                for (int off = 1; off < 32; off <<= 1) {
+                    const int t = __shfl_down_sync(0xFFFFFFFFu, incl, off);
+                    if (tid + off < 32) incl += t;
                 }
-                s_remaining = rem;  // rank of the wanted key inside digit d (1-based from the top)
-                s_prefix = prefix | ((unsigned long long)d << shift);
+                const int above = incl - own;  // keys in bins above this lane's
+                const int rem = s_remaining;
+                const bool mine = above < rem && rem <= incl;
+                const unsigned who = __ballot_sync(0xFFFFFFFFu, mine);
+                if (who == 0u) {  // fewer than rem keys in bins 1..255 and 0 together cannot happen while M > N; keep the serial walk's answer
+                    if (tid == 0) { s_remaining = rem - (incl - h8[0]); s_prefix = prefix; }
+                } else if (mine) {
+                    int r = rem - above, d = 7;
+                    for (; d > 0; --d) {
+                        if (h8[d] >= r) break;
+                        r -= h8[d];
+                    }
+                    s_remaining = r;  // rank of the wanted key inside digit d (1-based from the top)
+                    s_prefix = prefix | ((unsigned long long)(8 * tid + d) << shift);
+                }
             }
             __syncthreads();
         }

@@ -138,6 +138,11 @@ __device__ __forceinline__ float rsqrt_approx(float x) { float y; asm("rsqrt.app
 // disc + 1e-30 (== disc for disc >= 1): disc == 0 gives exactly 0, and disc < 0 gives NaN, which fails the
 // threshold comparison exactly like the reference's NaN does.
 // Pixel order: A/B index k = pixel k; cE = (c0, c2), cO = (c1, c3) as fp16 (integers <= 2040, exact).
+// RAW2 (fused NMS): out = tr - sqrt(disc) = 2R exactly (halving is exact, so RN(tr/2 - sqrt/2) = RN(tr - sqrt) / 2), NOT
+// thresholded: the response ring then holds doubled raw responses, the non-zero test and the window test compare
+// against the doubled threshold, and the half is taken when a candidate's key is written.  That removes a packed
+// multiply per pixel pair and a compare + select per pixel from the steady loop.
+template <bool RAW2 = false>
 __device__ __forceinline__ void shi_tomasi4(const float (&A)[4], const float (&B)[4], __half2 cE, __half2 cO, const float (&thr)[4],
                                             float (&out)[4]) {
     float cc[4], ab[4], t[4], ntt[4], dz[4];
@@ -159,10 +164,30 @@ __device__ __forceinline__ void shi_tomasi4(const float (&A)[4], const float (&B
         const u64 ns = mul2(nd, y), h = mul2(y, half);
         const u64 ne = fma2(ns, ns, nd);
         const u64 nsq = fma2(ne, h, ns);
-        const u64 r = fma2(nsq, half, mul2(pk(t[q], t[q + 1]), half));
-        float r0, r1; upk(r, r0, r1);
-        out[q] = r0 > thr[q] ? r0 : 0.0f;
-        out[q + 1] = r1 > thr[q + 1] ? r1 : 0.0f;
+        if (RAW2) {
+            const u64 r = add2(pk(t[q], t[q + 1]), nsq);
+            upk(r, out[q], out[q + 1]);
+        } else {
+            const u64 r = fma2(nsq, half, mul2(pk(t[q], t[q + 1]), half));
+            float r0, r1; upk(r, r0, r1);
+            out[q] = r0 > thr[q] ? r0 : 0.0f;
+            out[q + 1] = r1 > thr[q + 1] ? r1 : 0.0f;
+        }
+    }
+}
+
+// Harris response of four pixels: R = det - k * tr^2, det = a*b - c*c, every operation rounded once to fp32 in this order
+// (feature_extraction/corner_detection.cpp:196-199 evaluates the same expression in double; see vofront.h).
+__device__ __forceinline__ void harris4(const float (&A)[4], const float (&B)[4], __half2 cE, __half2 cO, const float (&thr)[4], float k,
+                                        float (&out)[4]) {
+    float cc[4];
+    cc[0] = fhfma_lo(cE, 0.f); cc[1] = fhfma_lo(cO, 0.f); cc[2] = fhfma_hi(cE, 0.f); cc[3] = fhfma_hi(cO, 0.f);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const float det = __fsub_rn(__fmul_rn(A[q], B[q]), cc[q]);
+        const float t = __fadd_rn(A[q], B[q]);
+        const float r = __fsub_rn(det, __fmul_rn(__fmul_rn(k, t), t));  // (k * trace) * trace, left to right
+        out[q] = r > thr[q] ? r : 0.0f;
     }
 }
 
@@ -203,10 +228,11 @@ __device__ __forceinline__ void sts4(const char* p, uint4 v) { *reinterpret_cast
 // stays in the warp's shared-memory ring and only candidate keys leave the SM (2 B/px + 8 B per candidate).
 // SRC = 0: gray input; 1: blurred input (vo_response); 2: a thresholded response map is streamed through the fused NMS
 // instead of being computed (vo_nms with windows 3 / 5: the suppression code under test is the production code).
-template <int SRC, bool GATHER, bool ALIGNED, int NMSH>
+template <int SRC, bool GATHER, bool ALIGNED, int NMSH, bool HARRIS = false>
 __global__ void __launch_bounds__(32 * NWARP, NMSH ? CTAS_PER_SM_FUSED : CTAS_PER_SM)
 k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows, int n_tasks) {
     constexpr bool FUSED = NMSH > 0, FROM_BLURRED = SRC == 1, FROM_R = SRC == 2;
+    static_assert(!HARRIS || !FUSED, "the Harris response takes the response-writing form");
     static_assert(!FROM_R || FUSED, "a response map can only feed the fused NMS");
     __shared__ __align__(16) char s_rings[NWARP][FUSED ? RING_BYTES_FUSED : RING_BYTES];
     const int lane = threadIdx.x & 31;
@@ -310,6 +336,9 @@ k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows, int n_tas
     char* const rring = ring + RRING_OFF;
     unsigned char* const s_item = reinterpret_cast<unsigned char*>(ring + ITEM_OFF);
     unsigned nz_prev[2] = {0u, 0u};
+    // ring scale and threshold of the window test: computed rows are doubled raw responses against 2 * threshold; a
+    // streamed response map (FROM_R) is already thresholded: plain values against 0
+    const float nms_thr = FROM_R ? 0.f : 2.0f * thr, key_scale = FROM_R ? 1.0f : 0.5f;
     const int nms_i_lo = max(max(NMSH, 35), ys_own), nms_i_hi = min(min(H - NMSH - 1, H - 35), ye_own - 1);
     const int nms_j_lo = max(NMSH, 37), nms_j_hi = min(W - NMSH - 1, W - 37);
     unsigned long long* __restrict__ cand = FUSED ? a.cand + (size_t)f * a.cand_cap : nullptr;
@@ -395,8 +424,10 @@ k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows, int n_tas
 #pragma unroll
                 for (int e4 = 0; e4 < 4; ++e4) {
                     const int j = j0 + e4;
-                    if (live && cv[e4] > m4[e4] && j >= nms_j_lo && j <= nms_j_hi) {
-                        const unsigned long long kk = ((unsigned long long)__float_as_uint(cv[e4]) << 32) | ((unsigned long long)i << 16) | (unsigned long long)j;
+                    // above the threshold and a strict maximum of its window: neighbours at or below the threshold count as zero
+                    // in the reference, and they are below this centre anyway
+                    if (live && cv[e4] > nms_thr && cv[e4] > m4[e4] && j >= nms_j_lo && j <= nms_j_hi) {
+                        const unsigned long long kk = ((unsigned long long)__float_as_uint(cv[e4] * key_scale) << 32) | ((unsigned long long)i << 16) | (unsigned long long)j;
                         if (nc == 0) key[0] = kk; else key[1] = kk;
                         ++nc;
                     }
@@ -576,13 +607,17 @@ k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows, int n_tas
                         const __half2 e2e4 = prmt_h2(eE, ReE, 0x5432), e3e5 = prmt_h2(eO, ReO, 0x5432);
                         const __half2 cE = __hsub2(__hadd2(LeO, em2e0), __hadd2(e2e4, e3e5));   // (c0, c2)
                         const __half2 cO = __hsub2(__hadd2(em2e0, em1e1), __hadd2(e3e5, ReE));  // (c1, c3)
-                        shi_tomasi4(A, B, cE, cO, thr4, out);
+                        if (HARRIS) harris4(A, B, cE, cO, thr4, a.harris_k, out);
+                        else shi_tomasi4<FUSED>(A, B, cE, cO, thr4, out);
                     }
                 }
                 if (FUSED) {
-                    // the thresholded row goes into the ring (zeros too: slots are reused); responses are > 0 or 0
+                    // the row goes into the ring as computed: doubled raw responses (zeros for rows outside 2 .. H-3: slots are
+                    // reused).  A group is a candidate group when any of its pixels exceeds the doubled threshold (fmaxf drops
+                    // the NaN of a negative discriminant).  Columns < 2 and > W-3, which the reference leaves at zero, hold
+                    // garbage here: no window of a centre inside the FREAK margins (columns 37 .. W-37) reaches them.
                     sts4(rrow + j * 512, make_uint4(__float_as_uint(out[0]), __float_as_uint(out[1]), __float_as_uint(out[2]), __float_as_uint(out[3])));
-                    nz[j] = __ballot_sync(FULL, fmaxf(fmaxf(out[0], out[1]), fmaxf(out[2], out[3])) > 0.f);
+                    nz[j] = __ballot_sync(FULL, fmaxf(fmaxf(out[0], out[1]), fmaxf(out[2], out[3])) > nms_thr);
                 } else if (STEADY || orow < ye) {
                     float* q = R_p + j * R_pitch;
                     asm volatile("" : "+l"(q));
@@ -651,6 +686,8 @@ bool stencil_can_fuse(int rows, int cols, int nms_window) {
 cudaError_t launch_stencil(const StencilArgs& a, int n_frames, int src, cudaStream_t st) {
     const int nms_h = a.nms_h;
     const bool from_blurred = src == STENCIL_SRC_BLURRED, from_R = src == STENCIL_SRC_RESPONSE;
+    const bool harris = a.response == VO_RESPONSE_HARRIS;
+    if ((a.response != VO_RESPONSE_SHI_TOMASI && !harris) || (harris && nms_h)) return cudaErrorInvalidValue;
     if (src < 0 || src > 2 || nms_h < 0 || nms_h > 2 || (from_R && !nms_h) ||
         (nms_h && (from_blurred || !stencil_can_fuse(a.rows, a.cols, 2 * nms_h + 1) || !a.cand || !a.cand_count)))
         return cudaErrorInvalidValue;
@@ -688,6 +725,18 @@ cudaError_t launch_stencil(const StencilArgs& a, int n_frames, int src, cudaStre
     } else if (nms_h == 2) {
         if (aligned) VO_LAUNCH(0, false, true, 2);
         else VO_LAUNCH(0, false, false, 2);
+    } else if (harris) {
+#define VO_LAUNCH_H(SR, GA, AL) k_stencil<SR, GA, AL, 0, true><<<grid, 32 * NWARP, 0, st>>>(a, n_strips, n_segs, seg_rows, (int)n_tasks)
+        if (from_blurred) {
+            if (gather) VO_LAUNCH_H(1, true, false);
+            else if (aligned) VO_LAUNCH_H(1, false, true);
+            else VO_LAUNCH_H(1, false, false);
+        } else {
+            if (gather) VO_LAUNCH_H(0, true, false);
+            else if (aligned) VO_LAUNCH_H(0, false, true);
+            else VO_LAUNCH_H(0, false, false);
+        }
+#undef VO_LAUNCH_H
     } else if (from_blurred) {
         if (gather) VO_LAUNCH(1, true, false, 0);
         else if (aligned) VO_LAUNCH(1, false, true, 0);

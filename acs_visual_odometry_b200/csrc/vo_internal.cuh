@@ -84,6 +84,7 @@ struct StencilArgs {
     uint8_t* blur; size_t blur_fstride, blur_pitch;     // may be null when from_blurred
     float* R; size_t R_fstride, R_pitch;                // floats; unused (may be null) when nms_h > 0
     int rows, cols; float threshold;
+    int response = 0; float harris_k = 0.f;             // VO_RESPONSE_*; HARRIS only with nms_h == 0
     // fused non-maximum suppression: half window 1 or 2 (0 = write R instead); candidates are appended to
     // cand[frame * cand_cap ...] with cand_count[frame] (zeroed by the caller) exactly as k_nms does
     int nms_h; unsigned long long* cand; int cand_cap; int* cand_count;
@@ -125,6 +126,10 @@ struct MatchArgs {
 };
 cudaError_t launch_match(const MatchArgs& a, int n_pairs, int max_n1, cudaStream_t s_);
 cudaError_t launch_match_finalize(const MatchArgs& a, int n_pairs, cudaStream_t s);
+cudaError_t launch_gradients_ref(const uint8_t* img, size_t pitch, int r0, int r1, int c0, int c1, float* jx, float* jy, float* jxy,
+                                 int cols, cudaStream_t st);
+cudaError_t launch_response_ref(const float* jx, const float* jy, const float* jxy, int cols, int r0, int r1, int c0, int c1,
+                                float threshold, int response, float harris_k, float* R, cudaStream_t st);
 cudaError_t launch_popc_peak(int mode, unsigned* scratch, int sms, int iters, cudaStream_t st, double* popc_per_launch);
 
 cudaError_t launch_pack_bytes(const uint8_t* bytes, int n, uint32_t* packed, int* flag, cudaStream_t s);

@@ -9,7 +9,7 @@ import numpy as np
 _LIB = None
 _PKG = Path(__file__).resolve().parent
 
-SYMBOLS = ["vo_host_fundamental", "vo_host_normalize_points", "vo_host_sampson", "vo_host_ransac", "vo_host_get_pose", "vo_host_read_gt_line",
+SYMBOLS = ["vo_host_fundamental", "vo_host_normalize_points", "vo_host_score", "vo_host_sampson", "vo_host_ransac", "vo_host_get_pose", "vo_host_read_gt_line",
            "vo_host_format_pose_csv", "vo_host_euler", "vo_host_read_gray", "vo_host_write_png", "vo_host_write_pgm",
            "vo_pipeline_run", "vo_pipeline_run_ex", "vo_host_last_error"]
 
@@ -64,6 +64,16 @@ def normalize_points(pts):
     n1, n2, T1, T2 = np.empty((len(pts), 3)), np.empty((len(pts), 3)), np.empty(9), np.empty(9)
     _ck(load_host_library().vo_host_normalize_points(_dp(pts), len(pts), _dp(n1), _dp(n2), _dp(T1), _dp(T2)))
     return n1, n2, T1.reshape(3, 3), T2.reshape(3, 3)
+
+
+def score(F, pts, threshold=1.0, force_scalar=False):
+    pts = _pts(pts)
+    F = np.ascontiguousarray(F, np.float64).reshape(9)
+    flags = np.empty(len(pts), np.uint8)
+    cnt = C.c_int()
+    _ck(load_host_library().vo_host_score(_dp(F), _dp(pts), len(pts), C.c_double(threshold), int(force_scalar),
+                                          flags.ctypes.data_as(C.POINTER(C.c_uint8)), C.byref(cnt)))
+    return flags, cnt.value
 
 
 def sampson(F, pts):

@@ -58,6 +58,16 @@ int vo_host_normalize_points(const double* pts, int n, double* n1, double* n2, d
     });
 }
 
+int vo_host_score(const double F[9], const double* pts, int n, double threshold, int force_scalar, uint8_t* flags, int* count) {
+    if (!F || !pts || !flags || !count || n < 0) return fail(-1, "null argument");
+    return guarded([&] {
+        std::vector<double> X0(n), X1(n), P0(n), P1(n);
+        for (int i = 0; i < n; ++i) { X0[i] = pts[4 * i]; X1[i] = pts[4 * i + 1]; P0[i] = pts[4 * i + 2]; P1[i] = pts[4 * i + 3]; }
+        *count = vo::score_correspondences(F, X0.data(), X1.data(), P0.data(), P1.data(), n, threshold, flags, force_scalar != 0);
+        return 0;
+    });
+}
+
 int vo_host_sampson(const double F[9], const double* pts, int n, double* err) {
     if (!F || !pts || !err || n < 0) return fail(-1, "null argument");
     const vo::Mat3 f = to_mat3(F);

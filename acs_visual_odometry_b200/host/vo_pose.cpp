@@ -185,25 +185,41 @@ PoseResult PoseUpdate::getPoseEx(const Mat3& F, const std::vector<Point2f>& poin
         n2[i] = Point2f{static_cast<float>((points2[i].x - K(0, 2)) / K(0, 0)), static_cast<float>((points2[i].y - K(1, 2)) / K(1, 1))};
     }
 
-    PoseResult best;
-    for (int c = 0; c < 4; ++c) {
-        const Mat3& R = *Rs[c];
-        const Vec3& tc = *ts[c];
-        int positive = 0;
-        for (size_t i = 0; i < n; ++i) {
-            double X[4];
-            triangulatePoint(R, tc, n1[i].x, n1[i].y, n2[i].x, n2[i].y, X);
-            for (double& v : X) v = static_cast<double>(static_cast<float>(v));  // triangulatePoints returns CV_32F for float input
-            const double w = X[3];
-            if (std::fabs(w) < 1e-6) continue;
-            const Vec3 P{{X[0] / w, X[1] / w, X[2] / w}};
-            const double z1 = P(2);
-            const Vec3 P2 = mul(R, P);
-            const double z2 = P2(2) + tc(2);
-            if (z1 > 0 && z2 > 0) ++positive;
+    // Cheirality votes (PoseUpdate.hpp:98-146).  The reference counts every point for every candidate and keeps the first
+    // candidate with the largest count.  Only that argmax (and the winner's count) is used afterwards, so the points are
+    // walked in blocks for all four candidates at once and a candidate is dropped as soon as it can no longer reach the
+    // leader even if every remaining point voted for it: the winner and its count are the reference's, and three of the
+    // four candidates typically stop after about half of the points.
+    int positive[4] = {0, 0, 0, 0};
+    bool alive[4] = {true, true, true, true};
+    const size_t block = 64;
+    for (size_t i0 = 0; i0 < n; i0 += block) {
+        const size_t i1 = std::min(n, i0 + block);
+        for (int c = 0; c < 4; ++c) {
+            if (!alive[c]) continue;
+            const Mat3& R = *Rs[c];
+            const Vec3& tc = *ts[c];
+            for (size_t i = i0; i < i1; ++i) {
+                double X[4];
+                triangulatePoint(R, tc, n1[i].x, n1[i].y, n2[i].x, n2[i].y, X);
+                for (double& v : X) v = static_cast<double>(static_cast<float>(v));  // triangulatePoints returns CV_32F for float input
+                const double w = X[3];
+                if (std::fabs(w) < 1e-6) continue;
+                const Vec3 P{{X[0] / w, X[1] / w, X[2] / w}};
+                const double z1 = P(2);
+                const Vec3 P2 = mul(R, P);
+                const double z2 = P2(2) + tc(2);
+                if (z1 > 0 && z2 > 0) ++positive[c];
+            }
         }
-        if (positive > best.positive_depth) { best.positive_depth = positive; best.R = R; best.t = tc; best.candidate = c; }
+        const int remaining = static_cast<int>(n - i1);
+        int lead = 0;
+        for (int c = 0; c < 4; ++c) if (alive[c]) lead = std::max(lead, positive[c]);
+        for (int c = 0; c < 4; ++c) if (alive[c] && positive[c] + remaining < lead) alive[c] = false;  // strictly behind: cannot even tie
     }
+    PoseResult best;
+    for (int c = 0; c < 4; ++c)
+        if (alive[c] && positive[c] > best.positive_depth) { best.positive_depth = positive[c]; best.R = *Rs[c]; best.t = *ts[c]; best.candidate = c; }
     if (det(best.R) < 0) best.R = scaled(best.R, -1.0);
     const double tnorm = norm(best.t);
     if (tnorm > 1e-6)

@@ -4,11 +4,88 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <iterator>
 #include <limits>
 #include <random>
 
+#if defined(__x86_64__) || defined(__i386__)
+#include <immintrin.h>
+#define VO_HAVE_AVX2_PATH 1
+#endif
+
 namespace vo {
+
+namespace {
+
+// Consensus scoring of one model over the scored correspondences: flag[i] = Sampson error < threshold, returns the count.
+// computeSampsonError (ransac.cpp:12-23) inlined, the same operations in the same order, every one rounded on its own
+// (the file is compiled with -ffp-contract=off and the AVX2 form uses separate multiplies and adds, never FMA), so the
+// scalar loop and the 4-wide loop give identical flags.
+int score_scalar(const double* F, const double* X0, const double* X1, const double* P0, const double* P1, int from, int n, double thr,
+                 unsigned char* flag) {
+    const double f00 = F[0], f01 = F[1], f02 = F[2], f10 = F[3], f11 = F[4], f12 = F[5], f20 = F[6], f21 = F[7], f22 = F[8];
+    int count = 0;
+    for (int i = from; i < n; ++i) {
+        const double x0 = X0[i], x1 = X1[i], p0 = P0[i], p1 = P1[i];
+        const double Fx0 = f00 * x0 + f01 * x1 + f02 * 1.0, Fx1 = f10 * x0 + f11 * x1 + f12 * 1.0, Fx2 = f20 * x0 + f21 * x1 + f22 * 1.0;
+        const double Ft0 = f00 * p0 + f10 * p1 + f20 * 1.0, Ft1 = f01 * p0 + f11 * p1 + f21 * 1.0;
+        const double e = p0 * Fx0 + p1 * Fx1 + 1.0 * Fx2;
+        const double den = Fx0 * Fx0 + Fx1 * Fx1 + Ft0 * Ft0 + Ft1 * Ft1;
+        const unsigned char in = (den >= 1e-12) & (e * e / den < thr);  // den < 1e-12: error = max
+        flag[i] = in;
+        count += in;
+    }
+    return count;
+}
+
+#ifdef VO_HAVE_AVX2_PATH
+__attribute__((target("avx2"))) int score_avx2(const double* F, const double* X0, const double* X1, const double* P0, const double* P1, int n,
+                                               double thr, unsigned char* flag) {
+    const __m256d f00 = _mm256_set1_pd(F[0]), f01 = _mm256_set1_pd(F[1]), f02 = _mm256_set1_pd(F[2]), f10 = _mm256_set1_pd(F[3]),
+                  f11 = _mm256_set1_pd(F[4]), f12 = _mm256_set1_pd(F[5]), f20 = _mm256_set1_pd(F[6]), f21 = _mm256_set1_pd(F[7]),
+                  f22 = _mm256_set1_pd(F[8]);
+    const __m256d eps = _mm256_set1_pd(1e-12), vthr = _mm256_set1_pd(thr);
+    int count = 0, i = 0;
+    for (; i + 4 <= n; i += 4) {
+        const __m256d x0 = _mm256_loadu_pd(X0 + i), x1 = _mm256_loadu_pd(X1 + i), p0 = _mm256_loadu_pd(P0 + i), p1 = _mm256_loadu_pd(P1 + i);
+        const __m256d Fx0 = _mm256_add_pd(_mm256_add_pd(_mm256_mul_pd(f00, x0), _mm256_mul_pd(f01, x1)), f02);
+        const __m256d Fx1 = _mm256_add_pd(_mm256_add_pd(_mm256_mul_pd(f10, x0), _mm256_mul_pd(f11, x1)), f12);
+        const __m256d Fx2 = _mm256_add_pd(_mm256_add_pd(_mm256_mul_pd(f20, x0), _mm256_mul_pd(f21, x1)), f22);
+        const __m256d Ft0 = _mm256_add_pd(_mm256_add_pd(_mm256_mul_pd(f00, p0), _mm256_mul_pd(f10, p1)), f20);
+        const __m256d Ft1 = _mm256_add_pd(_mm256_add_pd(_mm256_mul_pd(f01, p0), _mm256_mul_pd(f11, p1)), f21);
+        const __m256d e = _mm256_add_pd(_mm256_add_pd(_mm256_mul_pd(p0, Fx0), _mm256_mul_pd(p1, Fx1)), Fx2);
+        const __m256d den = _mm256_add_pd(_mm256_add_pd(_mm256_add_pd(_mm256_mul_pd(Fx0, Fx0), _mm256_mul_pd(Fx1, Fx1)), _mm256_mul_pd(Ft0, Ft0)),
+                                          _mm256_mul_pd(Ft1, Ft1));
+        const __m256d err = _mm256_div_pd(_mm256_mul_pd(e, e), den);
+        const __m256d in = _mm256_and_pd(_mm256_cmp_pd(den, eps, _CMP_GE_OQ), _mm256_cmp_pd(err, vthr, _CMP_LT_OQ));
+        const int m = _mm256_movemask_pd(in);
+        flag[i] = m & 1; flag[i + 1] = (m >> 1) & 1; flag[i + 2] = (m >> 2) & 1; flag[i + 3] = (m >> 3) & 1;
+        count += __builtin_popcount(m);
+    }
+    return count + score_scalar(F, X0, X1, P0, P1, i, n, thr, flag);
+}
+#endif
+
+bool use_avx2() {
+#ifdef VO_HAVE_AVX2_PATH
+    static const bool ok = __builtin_cpu_supports("avx2") && !std::getenv("VO_RANSAC_SCALAR");
+    return ok;
+#else
+    return false;
+#endif
+}
+
+}  // namespace
+
+// test hook (vo_host_score_models): both scoring loops on the same model
+int score_correspondences(const double F[9], const double* X0, const double* X1, const double* P0, const double* P1, int n, double thr,
+                          unsigned char* flag, bool force_scalar) {
+#ifdef VO_HAVE_AVX2_PATH
+    if (!force_scalar && use_avx2()) return score_avx2(F, X0, X1, P0, P1, n, thr, flag);
+#endif
+    return score_scalar(F, X0, X1, P0, P1, 0, n, thr, flag);
+}
 
 // ransac.cpp:12-23: (x'^T F x)^2 / ((Fx)_0^2 + (Fx)_1^2 + (F^T x')_0^2 + (F^T x')_1^2)
 double computeSampsonError(const Mat3& F, const Vec3& x, const Vec3& xp) {
@@ -135,19 +212,7 @@ RansacStats Ransac::run(FundamentalMatrix& model, const std::vector<PointPair>& 
         FundamentalMatrix tempModel;
         tempModel.fit(sample);  // fewer than 8 correspondences: F stays zero, every Sampson error is "max"
         const Mat3 F = tempModel.getMatrix();
-        const double f00 = F(0, 0), f01 = F(0, 1), f02 = F(0, 2), f10 = F(1, 0), f11 = F(1, 1), f12 = F(1, 2), f20 = F(2, 0), f21 = F(2, 1),
-                     f22 = F(2, 2);
-        int count = 0;
-        for (int i = 0; i < scored; ++i) {  // computeSampsonError inlined (same operations in the same order)
-            const double x0 = X0[i], x1 = X1[i], p0 = P0[i], p1 = P1[i];
-            const double Fx0 = f00 * x0 + f01 * x1 + f02 * 1.0, Fx1 = f10 * x0 + f11 * x1 + f12 * 1.0, Fx2 = f20 * x0 + f21 * x1 + f22 * 1.0;
-            const double Ft0 = f00 * p0 + f10 * p1 + f20 * 1.0, Ft1 = f01 * p0 + f11 * p1 + f21 * 1.0;
-            const double e = p0 * Fx0 + p1 * Fx1 + 1.0 * Fx2;
-            const double den = Fx0 * Fx0 + Fx1 * Fx1 + Ft0 * Ft0 + Ft1 * Ft1;
-            const unsigned char in = (den >= 1e-12) & (e * e / den < sampsonThreshold);  // den < 1e-12: error = max
-            flag[i] = in;
-            count += in;
-        }
+        const int count = score_correspondences(F.m, X0.data(), X1.data(), P0.data(), P1.data(), scored, sampsonThreshold, flag.data(), false);
         if (count > bestInliers) {  // the consensus set is materialised only when it is the best so far
             bestInliers = count;
             bestInlierSet.clear();

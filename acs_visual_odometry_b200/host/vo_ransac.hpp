@@ -41,6 +41,11 @@ public:
     const std::vector<PointPair>& getInliers() const { return inliers; }
 };
 
+// The consensus-scoring loop of Ransac::run on its own (flags + count for one model); AVX2 when the CPU has it, and the
+// scalar loop with force_scalar: both must agree bit for bit (tests/test_host.py).
+int score_correspondences(const double F[9], const double* X0, const double* X1, const double* P0, const double* P1, int n, double thr,
+                          unsigned char* flag, bool force_scalar);
+
 struct RansacStats {
     int iterations = 0;
     int best_inliers = 0;

@@ -61,7 +61,18 @@ typedef struct vo_params {
     int max_keypoints; /* N of non_maximum_suppression; <= the context's max_keypoints */
     float ratio;       /* Lowe ratio, 0.75f at every reference call site */
     int match_bits;    /* VO_MATCH_REF32 or VO_MATCH_FULL512 */
+    int response;      /* VO_RESPONSE_SHI_TOMASI (every preset) or VO_RESPONSE_HARRIS */
+    float harris_k;    /* k of R = det(M) - k * trace(M)^2 (feature_extraction/corner_detection.cpp:199); used by HARRIS only */
 } vo_params;
+
+/* Corner response.  SHI_TOMASI: the smaller eigenvalue, what the thread-pool and OpenCL paths compute
+ * (corner_detection_parallel.cpp:93-98).  HARRIS: det - k * trace^2, the formula of the reference's serial variant
+ * (feature_extraction/corner_detection.cpp:199), evaluated here in fp32 on the same structure tensor with the same
+ * absolute threshold semantics (values <= threshold become 0); the serial variant itself works in fp64 with a threshold
+ * relative to the image maximum, so this mode is pinned to the restatement in oracle/ only ("parity unpinned").
+ * HARRIS frames take the response-writing form of the stencil kernel followed by the NMS kernel. */
+#define VO_RESPONSE_SHI_TOMASI 0
+#define VO_RESPONSE_HARRIS 1
 
 int vo_params_preset(vo_params* p, int preset);
 
@@ -116,6 +127,22 @@ int vo_debug_fetch(vo_ctx* ctx, int slot, int what, void* dst);
  */
 int vo_blur(vo_ctx* ctx, const uint8_t* gray, int rows, int cols, uint8_t* blurred);
 int vo_response(vo_ctx* ctx, const uint8_t* blurred, int rows, int cols, float threshold, float* R);
+/* The same with the response selector of p (p->threshold, p->response, p->harris_k). */
+int vo_response_p(vo_ctx* ctx, const uint8_t* blurred, int rows, int cols, const vo_params* p, float* R);
+/* The reference's per-stage workers with their `interval` argument (rows [r0, r1), columns [c0, c1)), for callers that
+ * drive the stages themselves (vofront_adapter.hpp: class CornerDetectionParallel).  Matrices are packed rows x cols;
+ * only the rectangle the reference's worker writes is written, the rest of the output stays untouched.
+ *   vo_bgr2gray                  CornerDetectionParallel::custom_bgr2gray            corner_detection_parallel.cpp:14-28
+ *   vo_gradients                 ::direction_gradients_worker: rows r0+1 .. r1-2, columns c0+1 .. c1-2     :30-58
+ *   vo_response_from_gradients   ::shitomasi_corner_detection_worker: rows r0+2 .. r1-3, columns c0+2 .. c1-3, from
+ *                                ANY fp32 gradient matrices, the reference's summation order (p->threshold, p->response,
+ *                                p->harris_k; the reference's own `k` argument is unused, :61)            :61-105
+ * These run small one-thread-per-pixel kernels and synchronise; extraction never calls them (it runs the fused kernel). */
+int vo_bgr2gray(vo_ctx* ctx, const uint8_t* bgr, int rows, int cols, size_t pitch, uint8_t* gray);
+int vo_gradients(vo_ctx* ctx, const uint8_t* picture, int rows, int cols, size_t pitch, int r0, int r1, int c0, int c1, float* Jx,
+                 float* Jy, float* Jxy);
+int vo_response_from_gradients(vo_ctx* ctx, const float* Jx, const float* Jy, const float* Jxy, int rows, int cols, int r0, int r1,
+                               int c0, int c1, const vo_params* p, float* R);
 int vo_nms(vo_ctx* ctx, const float* R, int rows, int cols, int nms_window, int max_keypoints, float* kp_xy,
            int* n_out);
 int vo_describe(vo_ctx* ctx, const uint8_t* blurred, int rows, int cols, const float* kp_xy, int n,

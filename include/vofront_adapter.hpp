@@ -20,6 +20,7 @@
 // `thread_pool&` and `numThreads` are accepted and ignored: CUDA streams replace the pool.
 #pragma once
 #include <cstdint>
+#include <cstring>
 #include <memory>
 #include <stdexcept>
 #include <string>
@@ -39,51 +40,114 @@ inline void check(int rc, vo_ctx* ctx, const char* what) {
 // One GPU context, created once (the reference builds GPU_settings once in the VisualOdometry ctor,
 // VisualOdometry.cpp:14-23).  Copyable like the reference's struct of OpenCL handles.
 struct Context {
+    // What the adapter remembers about the descriptor sets it handed out: the reference's API returns descriptors as
+    // vector<vector<uint8_t>> and takes them back in the matcher, but the packed descriptors of the last n_slots
+    // extractions are still on the device.  match() packs the caller's rows on the host (it has to read them anyway),
+    // recognises a set this context produced by comparing ALL of its packed words with the copy kept here (so a recycled
+    // or edited vector can never alias a slot) and then matches slot against slot; any other set is uploaded in packed
+    // form, 64 bytes per descriptor instead of 512.
+    struct Resident { std::vector<uint32_t> packed; int n = -1; };  // 16 words per descriptor, as on the device
+    struct State { std::vector<Resident> slots; int next = 0; };
+
     std::shared_ptr<vo_ctx> ctx;
-    int max_rows = 0, max_cols = 0, max_keypoints = 0;
+    std::shared_ptr<State> state;
+    int max_rows = 0, max_cols = 0, max_keypoints = 0, n_slots = 0;
 
     Context() = default;
-    Context(int device, int rows, int cols, int max_kp = 2000, int n_slots = 4)
-        : max_rows(rows), max_cols(cols), max_keypoints(max_kp) {
+    Context(int device, int rows, int cols, int max_kp = 2000, int slots = 4)
+        : state(std::make_shared<State>()), max_rows(rows), max_cols(cols), max_keypoints(max_kp), n_slots(slots) {
         vo_ctx* c = nullptr;
-        const int rc = vo_create(&c, device, rows, cols, max_kp, n_slots);
+        const int rc = vo_create(&c, device, rows, cols, max_kp, slots);
         if (rc != VO_OK) throw std::runtime_error(std::string("vo_create: ") + vo_last_error(nullptr));
         ctx.reset(c, [](vo_ctx* p) { vo_destroy(p); });
+        state->slots.resize(slots);
     }
     vo_ctx* get() const { return ctx.get(); }
     bool fits(int rows, int cols, int kp) const { return ctx && rows <= max_rows && cols <= max_cols && kp <= max_keypoints; }
+    int take_slot() const { const int s = state->next; state->next = (s + 1) % n_slots; state->slots[s].n = -1; return s; }
+    // slot holding exactly these (packed) descriptors, or -1
+    int find(const std::vector<uint32_t>& packed, int n) const {
+        if (!state) return -1;
+        for (int s = 0; s < n_slots; ++s) {
+            const Resident& r = state->slots[s];
+            if (r.n == n && n > 0 && std::memcmp(r.packed.data(), packed.data(), 64 * (size_t)n) == 0) return s;
+        }
+        return -1;
+    }
 };
 
 // Process-wide context for the thread_pool overloads (which carry no GPU handle); grown on demand.
 inline Context& default_context(int rows, int cols, int max_kp) {
     static Context c;
     if (!c.fits(rows, cols, max_kp))
-        c = Context(0, rows > c.max_rows ? rows : c.max_rows, cols > c.max_cols ? cols : c.max_cols,
-                    max_kp > c.max_keypoints ? max_kp : c.max_keypoints);
+        c = Context(0, rows > c.max_rows ? rows : (c.max_rows > 64 ? c.max_rows : 64), cols > c.max_cols ? cols : (c.max_cols > 64 ? c.max_cols : 64),
+                    max_kp > c.max_keypoints ? max_kp : (c.max_keypoints > 2000 ? c.max_keypoints : 2000));
     return c;
 }
 
 using Descriptors = std::vector<std::vector<uint8_t>>;  // n x 512 bytes, one 0/1 byte per test (the reference layout)
 
+// 512 bytes of 0/1 <-> 16 little-endian words: bit (j & 31) of word (j >> 5) = test j (the device layout).
+// Eight 0/1 bytes become one byte with a multiply: byte i of x lands on bit 56 + i of x * 0x0102040810204080.
+inline bool pack_rows(const Descriptors& d, std::vector<uint32_t>& packed) {
+    packed.resize(16 * d.size());
+    uint8_t* out = reinterpret_cast<uint8_t*>(packed.data());
+    uint64_t bad = 0;
+    for (size_t k = 0; k < d.size(); ++k) {
+        if (d[k].size() != 512) throw std::runtime_error("descriptor rows must hold 512 bytes");
+        const uint8_t* row = d[k].data();
+        for (int w = 0; w < 64; ++w) {
+            uint64_t x;
+            std::memcpy(&x, row + 8 * w, 8);
+            bad |= x;
+            out[64 * k + w] = (uint8_t)((x * 0x0102040810204080ull) >> 56);
+        }
+    }
+    return (bad & 0xFEFEFEFEFEFEFEFEull) == 0;  // false: some byte is neither 0 nor 1
+}
+inline const uint64_t* expand_table() {
+    static uint64_t lut[256];
+    static bool ready = false;
+    if (!ready) {
+        for (int b = 0; b < 256; ++b) {
+            uint64_t v = 0;
+            for (int i = 0; i < 8; ++i) v |= (uint64_t)((b >> i) & 1) << (8 * i);
+            lut[b] = v;
+        }
+        ready = true;
+    }
+    return lut;
+}
+
+// One synchronous fetch of keypoints and PACKED descriptors (64 bytes each instead of 512 over PCIe); the reference's
+// byte-per-test rows are expanded on the host.
 inline std::pair<Descriptors, std::vector<cv::KeyPoint>> fetch(const Context& c, int slot) {
     int n = 0;
-    check(vo_frame_fetch(c.get(), slot, &n, nullptr, nullptr, nullptr), c.get(), "vo_frame_fetch");
-    std::vector<float> xy(2 * (size_t)(n > 0 ? n : 1));
-    std::vector<uint8_t> flat(512 * (size_t)(n > 0 ? n : 1));
-    if (n > 0) check(vo_frame_fetch(c.get(), slot, &n, xy.data(), flat.data(), nullptr), c.get(), "vo_frame_fetch");
+    std::vector<float> xy(2 * (size_t)c.max_keypoints);
+    Context::Resident& res = c.state->slots[slot];
+    res.n = -1;
+    res.packed.resize(16 * (size_t)c.max_keypoints);
+    check(vo_frame_fetch(c.get(), slot, &n, xy.data(), nullptr, res.packed.data()), c.get(), "vo_frame_fetch");
+    res.n = n;
+    const uint64_t* lut = expand_table();
+    const uint8_t* pk = reinterpret_cast<const uint8_t*>(res.packed.data());
     std::pair<Descriptors, std::vector<cv::KeyPoint>> out;
-    out.first.reserve(n);
+    out.first.resize(n);
     out.second.reserve(n);
     for (int k = 0; k < n; ++k) {
-        out.first.emplace_back(flat.begin() + 512 * (size_t)k, flat.begin() + 512 * (size_t)(k + 1));
+        std::vector<uint8_t>& row = out.first[k];
+        row.resize(512);
+        for (int w = 0; w < 64; ++w) std::memcpy(row.data() + 8 * w, &lut[pk[64 * (size_t)k + w]], 8);
         out.second.emplace_back(cv::Point2f(xy[2 * k], xy[2 * k + 1]), 1.0f);  // corner_detection_parallel.cpp:203
     }
     return out;
 }
 
-inline std::pair<Descriptors, std::vector<cv::KeyPoint>> extract(const Context& c, const cv::Mat& image, int preset, int slot = 0) {
+inline std::pair<Descriptors, std::vector<cv::KeyPoint>> extract(const Context& c, const cv::Mat& image, int preset, int slot = -1) {
     vo_params p;
     vo_params_preset(&p, preset);
+    if (slot < 0) slot = c.take_slot();  // round robin: the sets of the last n_slots frames stay matchable on the device
+    else c.state->slots[slot].n = -1;
     if (image.rows < 1 || image.cols < 1 || image.data == nullptr) throw std::runtime_error("empty image");
     const int ch = image.channels();
     if (ch == 3) check(vo_extract_bgr(c.get(), image.data, image.rows, image.cols, image.step, &p, slot), c.get(), "vo_extract_bgr");
@@ -95,19 +159,16 @@ inline std::pair<Descriptors, std::vector<cv::KeyPoint>> extract(const Context& 
 inline std::vector<std::pair<int, int>> match(const Context& c, const Descriptors& d1, const Descriptors& d2, float ratio,
                                               int match_bits = VO_MATCH_REF32) {
     if (d1.empty() || d2.empty()) return {};  // feature_matching_parallel.cpp:57
-    auto flatten = [](const Descriptors& d) {
-        std::vector<uint8_t> f(512 * d.size());
-        for (size_t k = 0; k < d.size(); ++k) {
-            if (d[k].size() != 512) throw std::runtime_error("descriptor rows must hold 512 bytes");
-            std::copy(d[k].begin(), d[k].end(), f.begin() + 512 * k);
-        }
-        return f;
-    };
-    const std::vector<uint8_t> f1 = flatten(d1), f2 = flatten(d2);
+    std::vector<uint32_t> p1, p2;
+    if (!pack_rows(d1, p1) || !pack_rows(d2, p2)) throw std::runtime_error("descriptor bytes must be 0 or 1");
     std::vector<int32_t> pairs(2 * d1.size());
     int n = 0;
-    check(vo_match_host(c.get(), f1.data(), (int)d1.size(), f2.data(), (int)d2.size(), 512, ratio, match_bits, pairs.data(),
-                        (int)d1.size(), &n), c.get(), "vo_match_host");
+    const int s1 = c.find(p1, (int)d1.size()), s2 = s1 >= 0 ? c.find(p2, (int)d2.size()) : -1;
+    if (s1 >= 0 && s2 >= 0)  // both sets came from this context and are still resident: nothing to upload
+        check(vo_match(c.get(), s1, s2, ratio, match_bits, pairs.data(), (int)d1.size(), &n), c.get(), "vo_match");
+    else
+        check(vo_match_host(c.get(), reinterpret_cast<const uint8_t*>(p1.data()), (int)d1.size(), reinterpret_cast<const uint8_t*>(p2.data()),
+                            (int)d2.size(), 64, ratio, match_bits, pairs.data(), (int)d1.size(), &n), c.get(), "vo_match_host");
     std::vector<std::pair<int, int>> out(n);
     for (int k = 0; k < n; ++k) out[k] = {pairs[2 * k], pairs[2 * k + 1]};
     return out;
@@ -187,7 +248,8 @@ inline std::vector<std::pair<int, int>> matchCustomBinaryDescriptorsThreadPool(
     int /*numThreads*/, float ratioThreshold = 0.75f) {
     if (desc1.empty() || desc2.empty()) return {};
     const int n = (int)(desc1.size() > desc2.size() ? desc1.size() : desc2.size());
-    return vofront::match(vofront::default_context(64, 64, n > 2000 ? n : 2000), desc1, desc2, ratioThreshold);
+    // the SAME process-wide context the thread_pool extraction overload uses (grown only if a set is larger than it holds)
+    return vofront::match(vofront::default_context(1, 1, n), desc1, desc2, ratioThreshold);
 }
 // Same, on an explicit context (what a VisualOdometry built around GPU_settings calls).
 inline std::vector<std::pair<int, int>> matchCustomBinaryDescriptorsThreadPool(
@@ -195,5 +257,96 @@ inline std::vector<std::pair<int, int>> matchCustomBinaryDescriptorsThreadPool(
     const GPU_settings& settings, float ratioThreshold = 0.75f) {
     return vofront::match(settings, desc1, desc2, ratioThreshold);
 }
+
+// Descriptor-only managers (feature_extraction_parallel.h:19, feature_extraction_parallel_GPU.h:54)
+inline std::vector<std::vector<uint8_t>> feature_extraction_manager(const cv::Mat& image, const GPU_settings& settings) {
+    return feature_extraction_manager_with_points(image, settings).first;
+}
+inline std::vector<std::vector<uint8_t>> feature_extraction_manager(cv::Mat& image, thread_pool& pool) {
+    return feature_extraction_manager_with_points(image, pool).first;
+}
+
+// ---- the reference's stage classes, same static signatures ------------------------------------------
+// feature_extraction_parallel/corner_detection_parallel.h:14-47.  They carry no GPU handle, so they run on the
+// process-wide context (vofront::default_context), like the thread_pool overloads above.
+inline size_t NUMBER_OF_THREADS = 4;   // kept for source compatibility; unused (CUDA streams replace the pool)
+inline int BLOCK_SIZE = 100;           // unused: the whole image is one pass (SURVEY.md section 0.2 on the strip race)
+constexpr float RESPONSE_THRESHOLD = 25000;
+
+struct bound2d { int start{}, end{}; };
+struct interval { bound2d cols, rows; };
+
+class CornerDetectionParallel {
+public:
+    // corner_detection_parallel.cpp:14-28
+    static cv::Mat custom_bgr2gray(cv::Mat& picture) {
+        if (picture.channels() != 3) throw std::runtime_error("custom_bgr2gray: 8-bit BGR expected");
+        vofront::Context& c = vofront::default_context(picture.rows, picture.cols, 2000);
+        cv::Mat out(picture.rows, picture.cols, CV_8UC1);
+        vofront::check(vo_bgr2gray(c.get(), picture.data, picture.rows, picture.cols, picture.step, out.data), c.get(), "vo_bgr2gray");
+        return out;
+    }
+    // :30-58.  Jx, Jy, Jxy: CV_32F matrices of the picture's size (the manager allocates them with cv::Mat::zeros,
+    // feature_extraction_parallel.cpp:229-231); only rows/columns strictly inside the interval are written.
+    static void direction_gradients_worker(const cv::Mat& picture, const interval& iv, cv::Mat& Jx, cv::Mat& Jy, cv::Mat& Jxy) {
+        vofront::Context& c = vofront::default_context(picture.rows, picture.cols, 2000);
+        for (const cv::Mat* m : {&Jx, &Jy, &Jxy})
+            if (m->rows != picture.rows || m->cols != picture.cols || m->step != (size_t)picture.cols * 4)
+                throw std::runtime_error("direction_gradients_worker: packed CV_32F matrices of the picture's size expected");
+        vofront::check(vo_gradients(c.get(), picture.data, picture.rows, picture.cols, picture.step, iv.rows.start, iv.rows.end, iv.cols.start,
+                                    iv.cols.end, reinterpret_cast<float*>(Jx.data), reinterpret_cast<float*>(Jy.data),
+                                    reinterpret_cast<float*>(Jxy.data)), c.get(), "vo_gradients");
+    }
+    // :61-105.  `k` is unused, as in the reference (its body computes the Shi-Tomasi response and thresholds with the
+    // RESPONSE_THRESHOLD constant).
+    static void shitomasi_corner_detection_worker(const cv::Mat& Jx, const cv::Mat& Jy, const cv::Mat& Jxy, const interval& iv, const float& /*k*/,
+                                                  std::vector<std::vector<float>>& R_array) {
+        const int rows = Jx.rows, cols = Jx.cols;
+        vofront::Context& c = vofront::default_context(rows, cols, 2000);
+        vo_params p;
+        vo_params_preset(&p, VO_PRESET_CPU_REF);
+        p.threshold = RESPONSE_THRESHOLD;
+        std::vector<float> flat((size_t)rows * cols, 0.0f);
+        vofront::check(vo_response_from_gradients(c.get(), reinterpret_cast<const float*>(Jx.data), reinterpret_cast<const float*>(Jy.data),
+                                                  reinterpret_cast<const float*>(Jxy.data), rows, cols, iv.rows.start, iv.rows.end,
+                                                  iv.cols.start, iv.cols.end, &p, flat.data()), c.get(), "vo_response_from_gradients");
+        for (int i = iv.rows.start + 2; i < iv.rows.end - 2; ++i)
+            for (int j = iv.cols.start + 2; j < iv.cols.end - 2; ++j) R_array[i][j] = flat[(size_t)i * cols + j];
+    }
+    // :166-208, keypoints in the order the manager hands them to FREAK (sorted by (y, x), feature_extraction_parallel.cpp:276-282)
+    static std::vector<cv::KeyPoint> non_maximum_suppression(const std::vector<std::vector<float>>& R_values, const int& n_rows,
+                                                             const int& n_cols, const int& k, const int& N) {
+        return vofront::non_maximum_suppression(vofront::default_context(n_rows, n_cols, N > 2000 ? N : 2000), R_values, n_rows, n_cols, k, N);
+    }
+};
+
+// feature_extraction_parallel/FREAK_feature_descriptor_parallel.h:104-110
+constexpr size_t KEY_POINTS_PER_TASK = 30;
+class FREAK_Parallel {
+public:
+    // FREAK_feature_descriptor_parallel.cpp:11-55
+    static float compute_orientation(const cv::KeyPoint& point, const cv::Mat& image) {
+        std::vector<float> ang;
+        vofront::FREAK_feature_description(vofront::default_context(image.rows, image.cols, 2000), {point}, image, &ang);
+        return ang.at(0);
+    }
+    // declared at .h:106 (its definition is commented out in the reference, .cpp:56-100: every keypoint, the start index unused)
+    static void FREAK_feature_description(const std::vector<cv::KeyPoint>& key_points, const cv::Mat blurred_gray_picture,
+                                          const size_t& /*starting_key_point_index*/, std::vector<std::vector<uint8_t>>& descriptor) {
+        FREAK_feature_description_worker(key_points, blurred_gray_picture, 0, descriptor, key_points.size(), key_points.size());
+    }
+    // .cpp:110-151: keypoints [start, min(num_of_keypoints, start + KEYPOINTS_PER_TASK)) into descriptor[i][0..511]
+    static void FREAK_feature_description_worker(const std::vector<cv::KeyPoint>& key_points, const cv::Mat& blurred_gray_picture,
+                                                 const size_t& starting_key_point_index, std::vector<std::vector<uint8_t>>& descriptor,
+                                                 const size_t& num_of_keypoints, const size_t& KEYPOINTS_PER_TASK = KEY_POINTS_PER_TASK) {
+        const size_t hi = num_of_keypoints < starting_key_point_index + KEYPOINTS_PER_TASK ? num_of_keypoints : starting_key_point_index + KEYPOINTS_PER_TASK;
+        if (hi <= starting_key_point_index) return;
+        const std::vector<cv::KeyPoint> part(key_points.begin() + starting_key_point_index, key_points.begin() + hi);
+        const int n = (int)part.size();
+        const auto d = vofront::FREAK_feature_description(vofront::default_context(blurred_gray_picture.rows, blurred_gray_picture.cols,
+                                                                                   n > 2000 ? n : 2000), part, blurred_gray_picture);
+        for (size_t q = 0; q < d.size(); ++q) descriptor[starting_key_point_index + q] = d[q];
+    }
+};
 
 #endif  // VOFRONT_NO_REFERENCE_NAMES

@@ -23,6 +23,10 @@ int vo_host_fundamental(const double* pts, int n, double F[9]);
 int vo_host_normalize_points(const double* pts, int n, double* n1, double* n2, double T1[9], double T2[9]);
 /* computeSampsonError (ransac.cpp:12-23) for n correspondences. */
 int vo_host_sampson(const double F[9], const double* pts, int n, double* err);
+/* The consensus-scoring loop of Ransac::run on its own (ransac.cpp:159-168): flags[i] = Sampson error of correspondence
+ * i < threshold, *count their number.  force_scalar 0: the AVX2 loop when the CPU has it; 1: the scalar loop.  Both give
+ * the same flags (separate multiplies and adds, no FMA). */
+int vo_host_score(const double F[9], const double* pts, int n, double threshold, int force_scalar, uint8_t* flags, int* count);
 /* Ransac::run (ransac.cpp:120-194).  seed 0 = std::random_device like the reference.  inliers (may be NULL)
  * receives the consensus set the final fit used, n_inliers its size (capacity n rows), iterations the count run. */
 int vo_host_ransac(const double* pts, int n, double probability, double sampson_threshold, int num_threads,

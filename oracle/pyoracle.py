@@ -51,6 +51,7 @@ class Oracle:
         lib.vo_oracle_blur.argtypes = [_u8p, C.c_int, C.c_int, _u8p]
         lib.vo_oracle_gradients.argtypes = [_u8p, C.c_int, C.c_int, _f32p, _f32p, _f32p]
         lib.vo_oracle_response.argtypes = [_u8p, C.c_int, C.c_int, C.c_float, _f32p]
+        lib.vo_oracle_response_harris.argtypes = [_u8p, C.c_int, C.c_int, C.c_float, C.c_float, _f32p]
         lib.vo_oracle_nms.argtypes = [_f32p, C.c_int, C.c_int, C.c_int, C.c_int, _f32p]
         lib.vo_oracle_nms.restype = C.c_int
         lib.vo_oracle_orientation.argtypes = [_u8p, C.c_int, C.c_int, C.c_float, C.c_float]
@@ -89,6 +90,12 @@ class Oracle:
         blurred = np.ascontiguousarray(blurred, np.uint8)
         out = np.empty(blurred.shape, np.float32)
         self.lib.vo_oracle_response(blurred, blurred.shape[0], blurred.shape[1], threshold, out)
+        return out
+
+    def response_harris(self, blurred, threshold, k):
+        blurred = np.ascontiguousarray(blurred, np.uint8)
+        out = np.empty(blurred.shape, np.float32)
+        self.lib.vo_oracle_response_harris(blurred, blurred.shape[0], blurred.shape[1], threshold, k, out)
         return out
 
     def nms(self, R, nms_window=5, max_keypoints=1500):

@@ -104,6 +104,39 @@ void vo_oracle_response(const uint8_t* b, int rows, int cols, float threshold, f
     free(jx); free(jy); free(jxy);
 }
 
+/* Harris response on the same structure tensor: R = det - k * trace^2 in fp32, one rounding per operation, left to
+ * right ((k * trace) * trace).  The formula is the reference's serial variant (feature_extraction/corner_detection.cpp:
+ * 196-199), which evaluates it in double with a threshold relative to the image maximum; no fp32 / absolute-threshold
+ * Harris exists in the reference, so this function has nothing to be pinned against: PARITY UNPINNED (restatement only). */
+void vo_oracle_response_harris(const uint8_t* b, int rows, int cols, float threshold, float k, float* R) {
+    const size_t n = (size_t)rows * cols;
+    float* jx = (float*)malloc(n * sizeof(float));
+    float* jy = (float*)malloc(n * sizeof(float));
+    float* jxy = (float*)malloc(n * sizeof(float));
+    vo_oracle_gradients(b, rows, cols, jx, jy, jxy);
+    memset(R, 0, n * sizeof(float));
+    for (int i = 2; i < rows - 2; ++i)
+        for (int j = 2; j < cols - 2; ++j) {
+            float sumjxy = 0, jx2 = 0, jy2 = 0;
+            for (int m = -2; m <= 2; ++m)
+                for (int q = -2; q <= 2; ++q) {
+                    const size_t at = (size_t)(i + m) * cols + (j + q);
+                    const float vx = jx[at], vy = jy[at], vxy = jxy[at];
+                    sumjxy += vxy;
+                    jx2 += vx * vx;
+                    jy2 += vy * vy;
+                }
+            const volatile float ab = jx2 * jy2, cc = sumjxy * sumjxy;  /* volatile: no contraction whatever the flags */
+            const volatile float det = ab - cc;
+            const volatile float trace = jx2 + jy2;
+            const volatile float kt = k * trace;
+            const volatile float ktt = kt * trace;
+            const float r = det - ktt;
+            R[(size_t)i * cols + j] = r > threshold ? r : 0;
+        }
+    free(jx); free(jy); free(jxy);
+}
+
 typedef struct { float r; int i, j; } cand_t;
 
 static int cand_desc(const void* pa, const void* pb) { /* (R, i, j) descending: std::priority_queue<tuple<float,int,int>> */

@@ -70,6 +70,44 @@ int main(int argc, char** argv) {
         auto kps = vofront::non_maximum_suppression(gpu_settings, R, rows, cols, 5, 1500);
         auto desc = vofront::FREAK_feature_description(gpu_settings, kps, blurred);
         dump_features(out, {desc, kps});
+        // --- 3b. the reference's stage classes with their static signatures, chained the way the manager chains them
+        // (feature_extraction_parallel.cpp:223-300), in TWO row intervals to exercise the interval argument
+        {
+            cv::Mat gray = CornerDetectionParallel::custom_bgr2gray(bgr);
+            cv::Mat bl = vofront::gaussian_blur7(gpu_settings, gray);
+            cv::Mat Jx = cv::Mat::zeros(rows, cols, CV_32F), Jy = cv::Mat::zeros(rows, cols, CV_32F), Jxy = cv::Mat::zeros(rows, cols, CV_32F);
+            const interval whole{{0, cols}, {0, rows}};
+            CornerDetectionParallel::direction_gradients_worker(bl, whole, Jx, Jy, Jxy);
+            std::vector<std::vector<float>> Rw(rows, std::vector<float>(cols, 0.0f));
+            const interval top{{0, cols}, {0, rows / 2 + 2}}, bottom{{0, cols}, {rows / 2 - 2, rows}};  // overlapping by the 2-row halo
+            CornerDetectionParallel::shitomasi_corner_detection_worker(Jx, Jy, Jxy, top, 0.05f, Rw);
+            CornerDetectionParallel::shitomasi_corner_detection_worker(Jx, Jy, Jxy, bottom, 0.05f, Rw);
+            auto kp2 = CornerDetectionParallel::non_maximum_suppression(Rw, rows, cols, 5, 1500);
+            std::vector<std::vector<uint8_t>> d2(kp2.size(), std::vector<uint8_t>(512));
+            for (size_t st = 0; st < kp2.size(); st += KEY_POINTS_PER_TASK)
+                FREAK_Parallel::FREAK_feature_description_worker(kp2, bl, st, d2, kp2.size());
+            dump_features(out, {d2, kp2});
+            // gradients of a sub-interval only: everything outside stays zero
+            cv::Mat Gx = cv::Mat::zeros(rows, cols, CV_32F), Gy = cv::Mat::zeros(rows, cols, CV_32F), Gxy = cv::Mat::zeros(rows, cols, CV_32F);
+            const interval sub{{10, cols - 20}, {5, 40}};
+            CornerDetectionParallel::direction_gradients_worker(bl, sub, Gx, Gy, Gxy);
+            put_i32(out, rows * cols);
+            out.write(reinterpret_cast<const char*>(Gx.data), (std::streamsize)rows * cols * 4);
+            out.write(reinterpret_cast<const char*>(Gy.data), (std::streamsize)rows * cols * 4);
+            out.write(reinterpret_cast<const char*>(Gxy.data), (std::streamsize)rows * cols * 4);
+            const float ang = kp2.empty() ? 0.0f : FREAK_Parallel::compute_orientation(kp2[0], bl);
+            out.write(reinterpret_cast<const char*>(&ang), 4);
+            // descriptor-only managers
+            auto donly = feature_extraction_manager(img1, gpu_settings);
+            put_i32(out, (int32_t)donly.size());
+            put_i32(out, donly == f1.first ? 1 : 0);
+            auto donly2 = feature_extraction_manager(bgr, pool1);
+            put_i32(out, donly2 == g1.first ? 1 : 0);
+            // a set the adapter did not produce (a copy with one bit flipped) must take the upload path and still be right
+            auto edited = f1.first;
+            edited[0][0] ^= 1;
+            dump_matches(out, matchCustomBinaryDescriptorsThreadPool(edited, f2.first, gpu_settings, 0.75f));
+        }
         // --- 4. error behaviour: empty input => empty result (feature_matching_parallel.cpp:57); bad input => std::runtime_error
         std::vector<std::vector<uint8_t>> none;
         put_i32(out, (int32_t)matchCustomBinaryDescriptorsThreadPool(none, f2.first, pool1, 8, 0.75f).size());

@@ -74,6 +74,30 @@ def test_adapter_matches_oracle(tmp_path, oracle, factory):
     kp, d, off = _read_features(buf, off)
     kp_o, d_o = oracle.extract(f1, 25000.0, 5, 1500)
     assert np.array_equal(kp, kp_o) and (d == d_o).mean() >= 0.9999
+    # 3b. the reference's stage classes (CornerDetectionParallel / FREAK_Parallel statics), response computed in two
+    # overlapping row intervals: the same keypoints and descriptors again
+    kp, d, off = _read_features(buf, off)
+    assert np.array_equal(kp, kp_o) and (d == d_o).mean() >= 0.9999
+    (npx,) = struct.unpack_from("<i", buf, off)
+    off += 4
+    G = np.frombuffer(buf, np.float32, 3 * npx, off).reshape(3, *f1.shape)
+    off += 12 * npx
+    bl = oracle.blur(f1)
+    jx, jy, jxy = oracle.gradients(bl)
+    want = np.zeros_like(G)
+    for k, a in enumerate((jx, jy, jxy)):
+        want[k, 6:39, 11:f1.shape[1] - 21] = a[6:39, 11:f1.shape[1] - 21]  # interval rows [5, 40), cols [10, cols-20): interior only
+    assert np.array_equal(G, want)
+    (ang,) = struct.unpack_from("<f", buf, off)
+    off += 4
+    assert abs(ang - oracle.orientation(bl, float(kp_o[0, 0]), float(kp_o[0, 1]))) <= 2e-6
+    n_desc, same1, same2 = struct.unpack_from("<iii", buf, off)
+    off += 12
+    assert n_desc == len(d1) and same1 == 1 and same2 == 1
+    m_edit, off = _read_matches(buf, off)
+    d1e = d1.copy()
+    d1e[0, 0] ^= 1
+    assert np.array_equal(m_edit, oracle.match(d1e, d2, 32, 0.75))
     # 4. empty input -> empty result; oversize image -> std::runtime_error
     n_empty, threw = struct.unpack_from("<ii", buf, off)
     assert n_empty == 0 and threw == 1

@@ -504,3 +504,94 @@ def test_full_size_configs(oracle):
         flat = np.full((2160, 3840), 77, np.uint8)
         assert (vo.blur(flat) == 77).all()
         assert np.array_equal(vo.blur(img[::-1, ::-1].copy()), vo.blur(img)[::-1, ::-1])
+
+
+# ---- response selector (vo_params.response / harris_k) and the per-stage workers of the façade classes ----
+def test_harris_response_and_extraction_vs_restatement(vo_small, oracle, factory, kitti_pair):
+    """HARRIS has no fp32 counterpart in the reference (its serial variant is fp64 with a relative threshold): the bar is
+    the restatement in oracle/vo_oracle.c - response map bit-exact, keypoints identical, descriptor bits as usual."""
+    from acs_visual_odometry_b200 import Params
+    from acs_visual_odometry_b200.api import RESPONSE_HARRIS
+    for name, img in images(factory, kitti_pair).items():
+        blurred = oracle.blur(img)
+        for thr, k in ((1e9, 0.04), (0.0, 0.06), (5e10, 0.0)):
+            p = Params(thr, 5, 1500, response=RESPONSE_HARRIS, harris_k=k)
+            got, want = vo_small.response_p(blurred, p), oracle.response_harris(blurred, thr, k)
+            assert bits_equal(got, want), report_mismatch(f"harris {name} thr={thr} k={k}", got, want)
+    for img, (thr, w, n) in ((factory[0], (2e9, 5, 1500)), (kitti_pair[0][0], (1e9, 3, 2000)), (kitti_pair[0][0], (1e9, 7, 800))):
+        p = Params(thr, w, n, response=RESPONSE_HARRIS, harris_k=0.04)
+        vo_small.extract(img, p, slot=0)
+        kp, d512, _ = vo_small.fetch(0)
+        blurred = oracle.blur(img)
+        kp_o = oracle.nms(oracle.response_harris(blurred, thr, 0.04), w, n)
+        assert len(kp_o) > 100 and np.array_equal(kp, kp_o)
+        d_o, _ = oracle.describe(blurred, kp_o)
+        assert (d512 == d_o).mean() >= DESC_AGREEMENT_MIN
+    with pytest.raises(Exception):
+        vo_small.extract(factory[0], Params(1e9, 5, 1500, response=7), slot=0)
+
+
+def response_from_gradients_cpu(jx, jy, jxy, interval, threshold):
+    """shitomasi_corner_detection_worker (corner_detection_parallel.cpp:61-105) in numpy float32: one rounding per
+    operation, the 25 terms accumulated row by row, left to right; only the interval's interior is written."""
+    r0, r1, c0, c1 = interval
+    R = np.zeros(jx.shape, np.float32)
+    i0, i1, j0, j1 = r0 + 2, r1 - 2, c0 + 2, c1 - 2
+    if i1 <= i0 or j1 <= j0:
+        return R
+    s = np.zeros((i1 - i0, j1 - j0), np.float32)
+    a = np.zeros_like(s)
+    b = np.zeros_like(s)
+    for m in range(-2, 3):
+        for n in range(-2, 3):
+            sl = (slice(i0 + m, i1 + m), slice(j0 + n, j1 + n))
+            s = s + jxy[sl]
+            a = a + jx[sl] * jx[sl]
+            b = b + jy[sl] * jy[sl]
+    det = a * b - s * s
+    tr = a + b
+    with np.errstate(invalid="ignore"):
+        sq = np.sqrt(tr * tr - np.float32(4) * det)
+        r = ((tr / np.float32(2)).astype(np.float64) - 0.5 * sq.astype(np.float64)).astype(np.float32)
+        R[i0:i1, j0:j1] = np.where(r > np.float32(threshold), r, np.float32(0))
+    return R
+
+
+def test_stage_workers_with_intervals(vo_small, oracle, factory):
+    from acs_visual_odometry_b200 import Params
+    img = factory[0]
+    rows, cols = img.shape
+    blurred = oracle.blur(img)
+    jx_o, jy_o, jxy_o = oracle.gradients(blurred)
+    # whole image = the oracle's (and the reference's) gradient matrices
+    for got, want in zip(vo_small.gradients(blurred), (jx_o, jy_o, jxy_o)):
+        assert bits_equal(got, want)
+    # a sub-interval writes its interior only, into whatever the caller's matrices hold
+    iv = (7, 61, 33, 200)
+    out = tuple(np.full((rows, cols), -5.0, np.float32) for _ in range(3))
+    vo_small.gradients(blurred, iv, out)
+    for got, want in zip(out, (jx_o, jy_o, jxy_o)):
+        exp = np.full((rows, cols), -5.0, np.float32)
+        exp[iv[0] + 1:iv[1] - 1, iv[2] + 1:iv[3] - 1] = want[iv[0] + 1:iv[1] - 1, iv[2] + 1:iv[3] - 1]
+        assert bits_equal(got, exp)
+    for empty in ((5, 7, 0, cols), (0, rows, 9, 10), (3, 3, 4, 4)):   # intervals without an interior: nothing happens
+        out = tuple(np.full((rows, cols), 3.0, np.float32) for _ in range(3))
+        vo_small.gradients(blurred, empty, out)
+        assert all((o == 3.0).all() for o in out)
+    # response from the image's gradients, whole image and as two strips = the fused kernel's map
+    p = Params(25000.0, 5, 1500)
+    whole = vo_small.response_from_gradients(jx_o, jy_o, jxy_o, p)
+    assert bits_equal(whole, oracle.response(blurred, 25000.0))
+    strips = np.zeros((rows, cols), np.float32)
+    vo_small.response_from_gradients(jx_o, jy_o, jxy_o, p, (0, rows // 2 + 2, 0, cols), strips)
+    vo_small.response_from_gradients(jx_o, jy_o, jxy_o, p, (rows // 2 - 2, rows, 0, cols), strips)
+    assert bits_equal(strips, whole)
+    # ANY fp32 gradients (non-integers, large magnitudes, a negative discriminant's NaN failing the threshold)
+    rng = np.random.default_rng(5)
+    g = [(rng.standard_normal((60, 90)) * s).astype(np.float32) for s in (300.0, 250.0, 40.0)]
+    for iv, thr in (((0, 60, 0, 90), 1000.0), ((4, 51, 10, 77), 0.0)):
+        got = vo_small.response_from_gradients(*g, Params(thr, 5, 1500), iv)
+        assert bits_equal(got, response_from_gradients_cpu(*g, iv, thr))
+    # custom_bgr2gray
+    bgr = rng.integers(0, 256, (50, 70, 3), dtype=np.uint8)
+    assert np.array_equal(vo_small.bgr2gray(bgr), oracle.bgr2gray(bgr))

@@ -291,3 +291,23 @@ def test_loop_oracle_skip_rules():
     # before any pair has succeeded the guard does fire in both modes
     _, log3, _ = _scripted_loop([(20, 5), (20, 12)], reuse_model=True)
     assert [e["status"] for e in log3] == ["first", "few_inliers", "ok"]
+
+
+def test_vector_scoring_equals_scalar_and_sampson():
+    """Ransac::run's consensus loop: the AVX2 form (no FMA) must flag exactly what the scalar form flags, and both must
+    be computeSampsonError < threshold; sizes around the vector width and a threshold that cuts through the data."""
+    rng = np.random.default_rng(8)
+    R, t = rot([0.2, 1, 0.1], 0.02), np.array([0.1, -0.02, 0.9])
+    F = host.fundamental(scene(40, R, t, seed=1))
+    for n in (0, 1, 3, 4, 5, 63, 64, 1001):
+        pts = scene(max(n, 1), R, t, seed=n, noise=0.6)[:n]
+        if n > 10:
+            pts[::7, 2:] += rng.normal(0, 3, pts[::7, 2:].shape)
+        for thr in (1.0, 0.2, 1e-6):
+            fv, cv_ = host.score(F, pts, thr, force_scalar=False)
+            fs, cs = host.score(F, pts, thr, force_scalar=True)
+            assert cv_ == cs == int(fs.sum()) and np.array_equal(fv, fs)
+            if n:
+                assert np.array_equal(fs.astype(bool), host.sampson(F, pts) < thr)
+    # a zero model: every denominator is below 1e-12, every error "max" (ransac.cpp:21)
+    assert host.score(np.zeros((3, 3)), scene(9, R, t), 1.0)[1] == 0
