@@ -361,8 +361,16 @@ int vo_sync(vo_ctx* c) {
 }
 
 void* vo_host_alloc(size_t bytes) {
+    // VO_HOST_ALLOC=wc asks for write-combined pages (the host only ever WRITES frames into these buffers; the copy
+    // engine reads them without snooping the CPU caches) - a tuning aid for the multi-GPU end-to-end rate, off by default
+    // because reading such memory from the CPU is very slow.
+    unsigned flags = cudaHostAllocDefault;
+    if (const char* e = getenv("VO_HOST_ALLOC")) {
+        if (strstr(e, "wc")) flags |= cudaHostAllocWriteCombined;
+        if (strstr(e, "portable")) flags |= cudaHostAllocPortable;
+    }
     void* p = nullptr;
-    if (cudaMallocHost(&p, bytes) != cudaSuccess) return nullptr;
+    if (cudaHostAlloc(&p, bytes, flags) != cudaSuccess) return nullptr;
     return p;
 }
 void vo_host_free(void* p) { if (p) cudaFreeHost(p); }
