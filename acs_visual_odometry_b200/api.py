@@ -76,6 +76,8 @@ def load_library():
     sig = {
         "vo_params_preset": (i, [P(_CParams), i]),
         "vo_create": (i, [P(vp), i, i, i, i, i]),
+        "vo_create_ex": (i, [P(vp), i, i, i, i, i, i]),
+        "vo_sequence_flags": (i, [vp, vp, i]),
         "vo_destroy": (None, [vp]),
         "vo_last_error": (C.c_char_p, [vp]),
         "vo_device_count": (i, []),
@@ -149,11 +151,11 @@ class PinnedBuffer:
 class VoFront:
     """One vo_ctx (one GPU)."""
 
-    def __init__(self, max_rows, max_cols, max_keypoints=2000, n_slots=4, device=0):
+    def __init__(self, max_rows, max_cols, max_keypoints=2000, n_slots=4, device=0, cand_cap=0):
         self.lib = load_library()
         self.max_rows, self.max_cols, self.max_keypoints, self.n_slots = max_rows, max_cols, max_keypoints, n_slots
         h = C.c_void_p()
-        rc = self.lib.vo_create(C.byref(h), device, max_rows, max_cols, max_keypoints, n_slots)
+        rc = self.lib.vo_create_ex(C.byref(h), device, max_rows, max_cols, max_keypoints, n_slots, cand_cap)
         if rc:
             raise VoError(rc, self.lib.vo_last_error(None).decode())
         self.h = h
@@ -328,6 +330,12 @@ class VoFront:
         self._ck(self.lib.vo_sequence_run(self.h, frames.ctypes.data_as(C.c_void_p), n, rows, cols, frames.strides[1],
                                           frames.strides[0], C.byref(params.c()), batch, C.byref(res)))
         return nk, kp, nm[:max(n - 1, 0)], (pr[:max(n - 1, 0)] if pr is not None else None)
+
+    def sequence_flags(self, n):
+        """Per-frame status bits of the last sequence call (bit 0: candidate list overflow)."""
+        f = np.zeros(n, np.int32)
+        self._ck(self.lib.vo_sequence_flags(self.h, _ptr(f), n))
+        return f
 
     def sequence_upload(self, frames):
         n, rows, cols = frames.shape

@@ -231,7 +231,12 @@ int vo_device_count(void) {
 }
 
 int vo_create(vo_ctx** out, int device, int max_rows, int max_cols, int max_keypoints, int n_slots) {
+    return vo_create_ex(out, device, max_rows, max_cols, max_keypoints, n_slots, 0);
+}
+
+int vo_create_ex(vo_ctx** out, int device, int max_rows, int max_cols, int max_keypoints, int n_slots, int cand_cap) {
     if (!out) return fail(nullptr, VO_ERR_BAD_ARG, "out is NULL");
+    if (cand_cap < 0 || (cand_cap > 0 && cand_cap < max_keypoints)) return fail(nullptr, VO_ERR_BAD_ARG, "cand_cap must be 0 (default) or >= max_keypoints");
     *out = nullptr;
     if (max_rows < 1 || max_cols < 1 || max_rows > 32768 || max_cols > 32768)
         return fail(nullptr, VO_ERR_BAD_ARG, "max_rows/max_cols out of range (1..32768)");
@@ -258,6 +263,7 @@ int vo_create(vo_ctx** out, int device, int max_rows, int max_cols, int max_keyp
     c->cand_cap = VO_CAND_CAP_MIN > 8 * max_keypoints ? VO_CAND_CAP_MIN : 8 * max_keypoints;
     const long long by_area = (long long)max_rows * max_cols / 32;
     if (by_area > c->cand_cap) c->cand_cap = (int)by_area;
+    if (cand_cap > 0) c->cand_cap = cand_cap;  // vo_create_ex: the caller knows its images (dense textures at a low threshold)
     c->sort_cap = 64;  // k_select sorts whole warps' worth (64 keys) in registers
     while (c->sort_cap < max_keypoints) c->sort_cap <<= 1;
     const size_t ts = (size_t)c->total_slots;
@@ -829,7 +835,15 @@ int vo_sequence_fetch(vo_ctx* c, vo_seq_result* out) {
         if (out->pairs) CK(c, cudaMemcpyAsync(out->pairs, c->d_seq_pairs, sizeof(int2) * (size_t)(n - 1) * c->max_kp, cudaMemcpyDeviceToHost, c->s_compute));
     }
     CK(c, cudaStreamSynchronize(c->s_compute));
+    c->last_seq_flags = flags;
     return check_flags(c, flags.data(), n);
+}
+
+int vo_sequence_flags(vo_ctx* c, int32_t* flags, int n) {
+    if (!c) return VO_ERR_BAD_ARG;
+    if (!flags || n < 0 || n > (int)c->last_seq_flags.size()) return fail(c, VO_ERR_BAD_ARG, "n exceeds the last sequence's frame count");
+    for (int k = 0; k < n; ++k) flags[k] = c->last_seq_flags[k];
+    return VO_OK;
 }
 
 int vo_sequence_run(vo_ctx* c, const uint8_t* frames, int n_frames, int rows, int cols, size_t pitch, size_t frame_stride,
@@ -894,6 +908,7 @@ int vo_sequence_run(vo_ctx* c, const uint8_t* frames, int n_frames, int rows, in
     CK(c, cudaStreamSynchronize(c->s_h2d));
     CK(c, cudaStreamSynchronize(c->s_compute));
     CK(c, cudaStreamSynchronize(c->s_d2h));
+    c->last_seq_flags.assign(flags, flags + n_frames);
     return check_flags(c, flags, n_frames);
 }
 

@@ -211,7 +211,11 @@ constexpr int RING_BYTES = 8192;
 // every lane's pixels: the window test of a compacted item needs its neighbours' columns), and the item list of a trip
 // (one byte per non-zero 4-pixel group: row-in-trip * 32 + lane) at 12288.
 constexpr int RRING_OFF = 8192, ITEM_OFF = 12288;
-constexpr int RING_BYTES_FUSED = 12288 + 128;
+// ... and a staging buffer of CBUF candidate keys at 12416: candidates are appended to the frame's list in batches, one
+// global atomic per flush instead of one per trip (the warp waits for the atomic's return value to place its keys: with
+// an atomic per trip that wait was 7 % of the kernel's warp-state samples, ncu source page of capture r02o).
+constexpr int CBUF = 32, CBUF_OFF = 12416;
+constexpr int RING_BYTES_FUSED = 12416 + CBUF * 8;
 __device__ __forceinline__ const char* slot_of(const char* pa, const char* pb, int c, int row_bytes) {
     const int s = c & 7;
     return ((s & 4) ? pb : pa) + (s & 3) * row_bytes;
@@ -335,13 +339,25 @@ k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows, int n_tas
     // the previous trip, the centre rows / columns this task decides and the frame's candidate list
     char* const rring = ring + RRING_OFF;
     unsigned char* const s_item = reinterpret_cast<unsigned char*>(ring + ITEM_OFF);
+    unsigned long long* __restrict__ cand = FUSED ? a.cand + (size_t)f * a.cand_cap : nullptr;
+    unsigned long long* const s_cbuf = reinterpret_cast<unsigned long long*>(ring + CBUF_OFF);
+    int cbuf_n = 0;  // keys staged in s_cbuf (warp-uniform)
+    auto flush_candidates = [&]() {  // whole warp
+        if (cbuf_n == 0) return;
+        __syncwarp();
+        int pos = 0;
+        if (lane == 0) pos = atomicAdd(a.cand_count + f, cbuf_n);
+        pos = __shfl_sync(FULL, pos, 0) + lane;
+        if (lane < cbuf_n && pos < a.cand_cap) cand[pos] = s_cbuf[lane];
+        __syncwarp();
+        cbuf_n = 0;
+    };
     unsigned nz_prev[2] = {0u, 0u};
     // ring scale and threshold of the window test: computed rows are doubled raw responses against 2 * threshold; a
     // streamed response map (FROM_R) is already thresholded: plain values against 0
     const float nms_thr = FROM_R ? 0.f : 2.0f * thr, key_scale = FROM_R ? 1.0f : 0.5f;
     const int nms_i_lo = max(max(NMSH, 35), ys_own), nms_i_hi = min(min(H - NMSH - 1, H - 35), ye_own - 1);
     const int nms_j_lo = max(NMSH, 37), nms_j_hi = min(W - NMSH - 1, W - 37);
-    unsigned long long* __restrict__ cand = FUSED ? a.cand + (size_t)f * a.cand_cap : nullptr;
     if (FUSED) {
 #pragma unroll
         for (int k = 0; k < 8; ++k) sts4(rring + k * 512 + lane * 16, make_uint4(0u, 0u, 0u, 0u));
@@ -434,12 +450,20 @@ k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows, int n_tas
                 }
                 const unsigned b1 = __ballot_sync(FULL, nc >= 1), b2 = __ballot_sync(FULL, nc >= 2);
                 const int n_new = __popc(b1) + __popc(b2);
-                if (n_new > 0) {  // warp-uniform: one atomic per round appends to the frame's candidate list
-                    int pos = 0;
-                    if (lane == 0) pos = atomicAdd(a.cand_count + f, n_new);
-                    pos = __shfl_sync(FULL, pos, 0) + __popc(b1 & lt) + __popc(b2 & lt);
-                    if (nc >= 1 && pos < a.cand_cap) cand[pos] = key[0];
-                    if (nc >= 2 && pos + 1 < a.cand_cap) cand[pos + 1] = key[1];
+                if (n_new > 0) {  // warp-uniform
+                    const int rel = __popc(b1 & lt) + __popc(b2 & lt);
+                    if (cbuf_n + n_new > CBUF) flush_candidates();
+                    if (n_new > CBUF) {  // a dense round: straight to the frame's list
+                        int pos = 0;
+                        if (lane == 0) pos = atomicAdd(a.cand_count + f, n_new);
+                        pos = __shfl_sync(FULL, pos, 0) + rel;
+                        if (nc >= 1 && pos < a.cand_cap) cand[pos] = key[0];
+                        if (nc >= 2 && pos + 1 < a.cand_cap) cand[pos + 1] = key[1];
+                    } else {
+                        if (nc >= 1) s_cbuf[cbuf_n + rel] = key[0];
+                        if (nc >= 2) s_cbuf[cbuf_n + rel + 1] = key[1];
+                        cbuf_n += n_new;
+                    }
                 }
             }
             __syncwarp();  // the next trip overwrites ring slots and the item list read above
@@ -646,6 +670,7 @@ k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows, int n_tas
             trip(std::false_type{}, t0);
         }
     }
+    if (FUSED) flush_candidates();
 }
 
 // custom_bgr2gray: saturate_cast<uchar>(0.114*B + 0.587*G + 0.299*R) in double, round-half-even

@@ -47,6 +47,8 @@ struct vo_ctx {
     int2* d_pairs = nullptr;     // [VO_MAX_BATCH][max_kp]
     int* d_nmatch = nullptr;     // [VO_MAX_BATCH]
     int last_match_n1 = 0;
+    std::vector<int> last_seq_flags;  // per-frame status bits of the last sequence call (vo_sequence_flags)
+    int cand_cap_request = 0;         // vo_create_ex: candidates per frame asked for (0 = the default formula)
 
     uint8_t* d_bytes = nullptr;  // scratch: 2 x max_kp x 512 unpacked descriptor bytes / BGR staging
     size_t bytes_cap = 0;

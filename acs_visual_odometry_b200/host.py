@@ -146,7 +146,7 @@ def write_pgm(path, img):
 
 
 STAT_KEYS = ["frames", "pairs_ok", "skipped_frames", "missing_frames", "rematched_pairs", "wall_s", "decode_s", "frontend_s",
-             "host_s", "compose_s", "ransac_iterations", "mean_keypoints", "mean_matches", "mean_inliers", "stale_model_pairs"]
+             "host_s", "compose_s", "ransac_iterations", "mean_keypoints", "mean_matches", "mean_inliers", "stale_model_pairs", "capacity_frames"]
 
 
 def pipeline_run(image_dir, num_images, pose_file, output_csv, num_threads=8, device=0, preset=1, batch=0, seed=1,

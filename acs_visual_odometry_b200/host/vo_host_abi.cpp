@@ -1,5 +1,6 @@
 // vo_host_abi.cpp — the C ABI of include/vohost.h over the host classes.
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <exception>
 #include <string>
@@ -173,6 +174,7 @@ int vo_pipeline_run_ex(int device, int num_threads, const char* image_dir, int n
         if (batch > 0) vo_.batch = batch;
         vo_.seed = seed;
         vo_.reuse_model = (flags & VO_PIPE_REUSE_MODEL) != 0;
+        if (const char* e = std::getenv("VO_CAND_CAP")) vo_.cand_cap = std::atoi(e);  // tuning / test aid: candidates per frame
         vo_.verbose = false;
         vo_.run(image_dir, static_cast<size_t>(num_images), pose_file, output_csv);
         const vo::RunStats& s = vo_.stats;
@@ -183,7 +185,7 @@ int vo_pipeline_run_ex(int device, int num_threads, const char* image_dir, int n
                                   double(s.ransac_iterations), s.mean_keypoints, s.mean_matches, s.mean_inliers};
             std::memcpy(stats, v, sizeof(v));
             stats[14] = double(s.stale_model_pairs);
-            stats[15] = 0;
+            stats[15] = double(s.capacity_frames);
         }
         return 0;
     });

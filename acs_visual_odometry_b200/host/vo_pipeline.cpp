@@ -59,7 +59,7 @@ void VisualOdometry::ensure_ctx(int rows, int cols) {
     if (ctx_ && rows <= ctx_rows_ && cols <= ctx_cols_) return;
     if (ctx_) { vo_destroy(ctx_); ctx_ = nullptr; }
     const int slots = 2 * (batch + 1) + 2;  // two chunk sets of batch+1 frames, plus two for on-demand pairs
-    const int rc = vo_create(&ctx_, device_, rows, cols, params.max_keypoints, slots);
+    const int rc = vo_create_ex(&ctx_, device_, rows, cols, params.max_keypoints, slots, cand_cap);
     if (rc != VO_OK) {
         const std::string msg = vo_last_error(nullptr);
         ctx_ = nullptr;
@@ -154,8 +154,10 @@ struct Chunk {
     std::vector<size_t> ids;      // frames held in `pixels`, in order; ids[0] is the previous readable frame
     std::vector<char> missing;    // per frame of [first, last)
     uint8_t* pixels = nullptr;    // pinned, (batch + 1) frames
-    std::vector<int32_t> nkp, nmatch, pairs;
-    std::vector<float> kp;
+    // results of vo_sequence_run, pinned as well: its device-to-host copies run asynchronously on their own stream and
+    // overlap the next chunk's kernels only into page-locked memory
+    int32_t* nkp = nullptr; int32_t* nmatch = nullptr; int32_t* pairs = nullptr;
+    float* kp = nullptr;
     double decode_s = 0;
 };
 
@@ -187,9 +189,17 @@ void VisualOdometry::run(const std::string image_dir, const size_t num_images, c
     const size_t nchunks = num_images > 1 ? (num_images - 1 + batch - 1) / batch : 0;
 
     Chunk chunks[3];
+    auto free_chunks = [&] {
+        for (Chunk& c : chunks) { vo_host_free(c.pixels); vo_host_free(c.nkp); vo_host_free(c.nmatch); vo_host_free(c.pairs); vo_host_free(c.kp); }
+    };
     for (Chunk& c : chunks) {
-        c.pixels = static_cast<uint8_t*>(vo_host_alloc(fbytes * (batch + 1)));
-        if (!c.pixels) throw std::runtime_error("vo_host_alloc failed");
+        const size_t nf = static_cast<size_t>(batch) + 1;
+        c.pixels = static_cast<uint8_t*>(vo_host_alloc(fbytes * nf));
+        c.nkp = static_cast<int32_t*>(vo_host_alloc(sizeof(int32_t) * nf));
+        c.nmatch = static_cast<int32_t*>(vo_host_alloc(sizeof(int32_t) * nf));
+        c.kp = static_cast<float*>(vo_host_alloc(sizeof(float) * nf * maxkp * 2));
+        c.pairs = static_cast<int32_t*>(vo_host_alloc(sizeof(int32_t) * nf * maxkp * 2));
+        if (!c.pixels || !c.nkp || !c.nmatch || !c.kp || !c.pairs) { free_chunks(); throw std::runtime_error("vo_host_alloc failed"); }
     }
     std::vector<uint8_t> anchor(fbytes);  // pixels of the query frame while a failure streak lasts
     size_t anchor_id = static_cast<size_t>(-1);
@@ -233,15 +243,28 @@ void VisualOdometry::run(const std::string image_dir, const size_t num_images, c
     // ---- stage 2: the GPU front end on every frame of the chunk, consecutive pairs matched
     auto frontend = [&](Chunk& c) {
         const int n = static_cast<int>(c.ids.size());
-        c.nkp.assign(n, 0);
-        c.nmatch.assign(n > 1 ? n - 1 : 0, 0);
-        c.kp.resize(static_cast<size_t>(n) * maxkp * 2);
-        c.pairs.resize(static_cast<size_t>(n > 1 ? n - 1 : 0) * maxkp * 2);
+        std::fill(c.nkp, c.nkp + n, 0);
+        std::fill(c.nmatch, c.nmatch + (n > 1 ? n - 1 : 0), 0);
         if (n < 2) return;
         const double t0 = now_s();
-        vo_seq_result out{c.nkp.data(), c.kp.data(), c.nmatch.data(), c.pairs.data()};
-        check(ctx_, vo_sequence_run(ctx_, c.pixels, n, rows, cols, static_cast<size_t>(cols), fbytes, &params, batch + 1, &out),
-              "vo_sequence_run");
+        vo_seq_result out{c.nkp, c.kp, c.nmatch, c.pairs};
+        const int rc = vo_sequence_run(ctx_, c.pixels, n, rows, cols, static_cast<size_t>(cols), fbytes, &params, batch + 1, &out);
+        if (rc == VO_ERR_CAPACITY) {
+            // a frame had more NMS candidates than the context holds (vo_create_ex sizes the list): its keypoints would come
+            // from an arbitrary subset, so the frame is treated like one without features - its pairs carry no matches and
+            // take the reference's "too few matches" branch (VisualOdometry.cpp:108-115) - instead of ending the run
+            std::vector<int32_t> flags(n);
+            check(ctx_, vo_sequence_flags(ctx_, flags.data(), n), "vo_sequence_flags");
+            for (int k = 0; k < n; ++k) {
+                if (!(flags[k] & 1)) continue;
+                ++stats.capacity_frames;
+                c.nkp[k] = 0;
+                if (k > 0) c.nmatch[k - 1] = 0;
+                if (k + 1 < n) c.nmatch[k] = 0;
+            }
+        } else {
+            check(ctx_, rc, "vo_sequence_run");
+        }
         stats.frontend_s += now_s() - t0;
     };
 
@@ -362,10 +385,10 @@ void VisualOdometry::run(const std::string image_dir, const size_t num_images, c
         }
         if (nchunks) { stats.host_s += fut_host.get(); compose(nchunks - 1); }
     } catch (...) {
-        for (Chunk& c : chunks) vo_host_free(c.pixels);
+        free_chunks();
         throw;
     }
-    for (Chunk& c : chunks) vo_host_free(c.pixels);
+    free_chunks();
 
     if (!writePoseCSV(output_csv, estimated_poses_)) std::fprintf(stderr, "Failed to open output CSV file.\n");
     else if (verbose) std::printf("Wrote estimated poses to: %s\n", output_csv.c_str());

@@ -32,6 +32,7 @@ struct KeyPoint {  // the fields of cv::KeyPoint the pipeline uses
 
 struct RunStats {
     size_t frames = 0, pairs_ok = 0, skipped_frames = 0, missing_frames = 0, respeculated = 0;
+    size_t capacity_frames = 0;    // frames whose NMS candidate list overflowed: treated as frames without features
     size_t stale_model_pairs = 0;  // reuse_model only: pairs whose pose came from the previous pair's model
     double wall_s = 0;        // whole run
     double decode_s = 0;      // sum over chunks, overlapped with the rest
@@ -58,6 +59,7 @@ public:
     // knobs the reference hard-codes
     vo_params params;            // preset VO_PRESET_VO_GPU_REF (what VisualOdometry links), ratio 0.75, REF32
     int batch = 64;              // frames per chunk
+    int cand_cap = 0;            // NMS candidates per frame the context holds (vo_create_ex; 0 = its default formula)
     std::uint64_t seed = 0;      // 0: std::random_device per pair, like the reference; else pair i uses seed + i
     double ransac_probability = 0.99, sampson_threshold = 1.0;  // VisualOdometry.cpp:125
     // The reference keeps ONE FundamentalMatrix across frames (VisualOdometry.cpp:49); when a RANSAC run ends without a

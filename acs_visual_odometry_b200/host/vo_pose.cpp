@@ -191,35 +191,40 @@ PoseResult PoseUpdate::getPoseEx(const Mat3& F, const std::vector<Point2f>& poin
     //  * (R, -t) needs no triangulation of its own.  Its DLT matrix is the one of (R, t) with the last column negated
     //    (the rows of view 1 have a zero there), so its null vector is (x, y, z, -w): the homogenised point, z1 and z2
     //    all change sign exactly, and its vote is "both depths negative" on the triangulation of (R, t);
-    //  * only the argmax and its count are used afterwards, so the points are walked in blocks and a candidate is
-    //    dropped as soon as it can no longer reach the leader even if every remaining point voted for it.
+    //  * only the argmax and its count are used afterwards, so a rotation is dropped as soon as neither of its candidates
+    //    can reach the leader's count even if every remaining point voted for it (its partial counts are then below the
+    //    winner's and cannot be chosen).
     int positive[4] = {0, 0, 0, 0};
-    bool alive[4] = {true, true, true, true};
-    const size_t block = 64;
-    for (size_t i0 = 0; i0 < n; i0 += block) {
-        const size_t i1 = std::min(n, i0 + block);
-        for (int c = 0; c < 4; c += 2) {
-            if (!alive[c] && !alive[c + 1]) continue;
-            const Mat3& R = *Rs[c];
-            const Vec3& tc = *ts[c];  // +t; candidate c + 1 is (R, -t)
-            for (size_t i = i0; i < i1; ++i) {
-                double X[4];
-                triangulatePoint(R, tc, n1[i].x, n1[i].y, n2[i].x, n2[i].y, X);
-                for (double& v : X) v = static_cast<double>(static_cast<float>(v));  // triangulatePoints returns CV_32F for float input
-                const double w = X[3];
-                if (std::fabs(w) < 1e-6) continue;
-                const Vec3 P{{X[0] / w, X[1] / w, X[2] / w}};
-                const double z1 = P(2);
-                const Vec3 P2 = mul(R, P);
-                const double z2 = P2(2) + tc(2);
-                if (z1 > 0 && z2 > 0) ++positive[c];
-                if (z1 < 0 && z2 < 0) ++positive[c + 1];
-            }
+    auto vote = [&](int c, size_t i0, size_t i1) {  // candidates c = (R, +t) and c + 1 = (R, -t) over points [i0, i1)
+        const Mat3& R = *Rs[c];
+        const Vec3& tc = *ts[c];
+        for (size_t i = i0; i < i1; ++i) {
+            double X[4];
+            triangulatePoint(R, tc, n1[i].x, n1[i].y, n2[i].x, n2[i].y, X);
+            for (double& v : X) v = static_cast<double>(static_cast<float>(v));  // triangulatePoints returns CV_32F for float input
+            const double w = X[3];
+            if (std::fabs(w) < 1e-6) continue;
+            const Vec3 P{{X[0] / w, X[1] / w, X[2] / w}};
+            const double z1 = P(2);
+            const Vec3 P2 = mul(R, P);
+            const double z2 = P2(2) + tc(2);
+            if (z1 > 0 && z2 > 0) ++positive[c];
+            if (z1 < 0 && z2 < 0) ++positive[c + 1];
         }
-        const int remaining = static_cast<int>(n - i1);
-        int lead = 0;
-        for (int c = 0; c < 4; ++c) if (alive[c]) lead = std::max(lead, positive[c]);
-        for (int c = 0; c < 4; ++c) if (alive[c] && positive[c] + remaining < lead) alive[c] = false;  // strictly behind: cannot even tie
+    };
+    // the first block for both rotations, then the leading rotation to the end, then the other one only for as long as
+    // one of its candidates could still reach (or tie) the leader's final count
+    const size_t block = 64, first = std::min(n, block);
+    vote(0, 0, first);
+    vote(2, 0, first);
+    const int lead_pair = std::max(positive[2], positive[3]) > std::max(positive[0], positive[1]) ? 2 : 0, other = 2 - lead_pair;
+    vote(lead_pair, first, n);
+    const int lead = std::max(positive[lead_pair], positive[lead_pair + 1]);
+    bool alive[4] = {true, true, true, true};
+    for (size_t i0 = first; i0 < n; i0 += block) {
+        const int remaining = static_cast<int>(n - i0);
+        if (std::max(positive[other], positive[other + 1]) + remaining < lead) { alive[other] = alive[other + 1] = false; break; }
+        vote(other, i0, std::min(n, i0 + block));
     }
     PoseResult best;
     for (int c = 0; c < 4; ++c)

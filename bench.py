@@ -480,7 +480,7 @@ def main():
                         "time (barrier before every repetition, best of 5, CUDA events); floor = frames / the slowest rank's bare copy",
                 "timing": "wall clock around the synchronous C-ABI call vo_sequence_run, max over ranks"},
         "gpu_launches": int(launches), "clocks": clocks, "host_binding": numa, "host_link": link,
-        "ms_per_step_by_rank": [round(x, 4) for x in ms_ranks],
+        "ms_per_step_by_rank": [round(x, 4) for x in ms_ranks], "sm_mhz_by_rank": all_ranks(clocks.get("sm_mhz") or 0.0),
         "roofline": roofline, "roofline_unfused": unfused, "roofline_matcher": matcher if args.config != 2 else None,
         "kernel_ms_per_step": kernel_ms,
         "keypoints_per_frame": float(np.mean(nk)), "matches_per_pair": float(np.mean(nm)) if len(nm) else 0.0,

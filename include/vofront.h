@@ -85,6 +85,10 @@ int vo_params_preset(vo_params* p, int preset);
  * keypoints, packed descriptors), 2 .. 2048; batched calls use consecutive slots modulo n_slots and take at most
  * 1024 frames (or pairs) per call or chunk. */
 int vo_create(vo_ctx** out, int device, int max_rows, int max_cols, int max_keypoints, int n_slots);
+/* The same with the capacity of the per-frame NMS candidate list chosen by the caller (0 = the default: max(32768,
+ * 8 * max_keypoints, max_rows * max_cols / 32)).  The reference's heap has no limit (corner_detection_parallel.cpp:
+ * 170-196); here a frame with more candidates than this is reported with VO_ERR_CAPACITY, never truncated silently. */
+int vo_create_ex(vo_ctx** out, int device, int max_rows, int max_cols, int max_keypoints, int n_slots, int cand_cap);
 void vo_destroy(vo_ctx* ctx);
 const char* vo_last_error(const vo_ctx* ctx);
 int vo_device_count(void);
@@ -185,6 +189,10 @@ int vo_sequence_upload(vo_ctx* ctx, const uint8_t* frames, int n_frames, int row
                        size_t frame_stride);
 int vo_sequence_run_resident(vo_ctx* ctx, const vo_params* p, int batch);
 int vo_sequence_fetch(vo_ctx* ctx, vo_seq_result* out);
+/* Per-frame status bits of the last vo_sequence_run / vo_sequence_fetch call (bit 0: that frame's candidate list
+ * overflowed, the call returned VO_ERR_CAPACITY; all other frames' results are complete and were copied out), so that a
+ * caller can treat the frame like a failed one instead of giving up the sequence. */
+int vo_sequence_flags(vo_ctx* ctx, int32_t* flags, int n);
 
 /* ---- measurement hooks ------------------------------------------------------------------------ */
 /* CUDA-event timing on the context's own compute stream. */

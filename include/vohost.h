@@ -56,7 +56,8 @@ int vo_pipeline_run(int device, int num_threads, const char* image_dir, int num_
                     const char* output_csv, int preset, int batch, uint64_t seed, double* stats);
 /* The same with flags: VO_PIPE_REUSE_MODEL keeps one FundamentalMatrix across frames like the reference does
  * (VisualOdometry.cpp:49): a pair whose RANSAC run ends without a consensus set of 8 is then processed with the
- * previous pair's F and inliers (ransac.cpp:95-96 returns early) instead of being skipped.  stats[14] counts them. */
+ * previous pair's F and inliers (ransac.cpp:95-96 returns early) instead of being skipped.  stats[14] counts them;
+ * stats[15] counts frames whose NMS candidate list overflowed (treated as frames without features, not as an error). */
 #define VO_PIPE_REUSE_MODEL 1
 int vo_pipeline_run_ex(int device, int num_threads, const char* image_dir, int num_images, const char* pose_file,
                        const char* output_csv, int preset, int batch, uint64_t seed, int flags, double* stats);

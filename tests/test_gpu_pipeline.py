@@ -130,3 +130,41 @@ def test_skip_rules_against_sequential_oracle(tmp_path, scene24, oracle, reuse_m
     # pair is discarded and the pair (last valid, i) recomputed (vo_pipeline.cpp, compose stage)
     expect_rematch = sum(1 for i, e in enumerate(log) if "query" in e and e["query"] != max(j for j in range(i) if j not in missing))
     assert expect_rematch >= 4 and st["rematched_pairs"] == expect_rematch
+
+
+def test_candidate_overflow_is_a_failed_frame_not_a_failed_run(tmp_path, scene24, oracle):
+    """A frame with more NMS candidates than the context holds (uniform noise: a local maximum every few pixels) is
+    reported by the C ABI (VO_ERR_CAPACITY + per-frame flags) and handled by the pipeline like a frame without
+    features; every other frame's result is unaffected."""
+    from acs_visual_odometry_b200 import Params, VoError, VoFront
+    frames, gt = scene24
+    fr = [f.copy() for f in frames[:8]]
+    fr[4] = np.random.default_rng(3).integers(0, 256, fr[4].shape, dtype=np.uint8)
+    stack = np.stack(fr)
+    p = Params.vo_gpu_ref()
+    with VoFront(*stack.shape[1:], p.max_keypoints, 2 * 8, cand_cap=200000) as vo:   # vo_create_ex: room for every frame
+        nk, kp, nm, pr = vo.sequence_run(stack, p, 8)
+        assert vo.sequence_flags(8).tolist() == [0] * 8
+        kp_o, _ = oracle.extract(fr[4], 20000.0, 3, 2000)
+        assert nk[4] == len(kp_o) == 2000 and np.array_equal(kp[4, :2000], kp_o)
+    # candidates per frame: the noise frame has several times more than the scene frames; a capacity between the two
+    cands = [len(oracle.nms(oracle.response(oracle.blur(f), 20000.0), 3, 1 << 20)) for f in fr]
+    cap = int(0.5 * (max(c for i, c in enumerate(cands) if i != 4) + cands[4]))
+    assert cands[4] > 2 * max(c for i, c in enumerate(cands) if i != 4) and cap >= p.max_keypoints, cands
+    with VoFront(*stack.shape[1:], p.max_keypoints, 2 * 8, cand_cap=cap) as vo:
+        with pytest.raises(VoError) as e:
+            vo.sequence_run(stack, p, 8)
+        assert e.value.code == -3
+        assert vo.sequence_flags(8).tolist() == [0, 0, 0, 0, 1, 0, 0, 0]
+    image_dir, pose_file = write_sequence(tmp_path, fr, gt[:8])
+    import os
+    os.environ["VO_CAND_CAP"] = str(cap)
+    try:
+        st = host.pipeline_run(image_dir, 8, pose_file, tmp_path / "est.csv", num_threads=8, batch=5, seed=SEED)
+    finally:
+        del os.environ["VO_CAND_CAP"]
+    assert st["capacity_frames"] == 1 and st["skipped_frames"] == 1 and st["pairs_ok"] == 6
+    blank = [f if i != 4 else np.full_like(f, 128) for i, f in enumerate(fr)]
+    want, log = run_loop(blank, gt[:8], *oracle_stages(oracle, 8, SEED))
+    assert [e["status"] for e in log[1:]] == ["ok", "ok", "ok", "few_matches", "ok", "ok", "ok"]
+    np.testing.assert_allclose(read_csv_poses(tmp_path / "est.csv"), want, rtol=2e-8, atol=1e-9)

@@ -24,4 +24,7 @@ with VoFront(376, 1241, p.max_keypoints, 2 * batch) as vo:
         vo.sequence_run_resident(p, batch)
     vo.sync()
     nk, _, nm, _ = vo.sequence_fetch(want_kp=False, want_pairs=False)
+    # the response-writing form of the stencil kernel is not part of the step: launch it alone so that a capture of this
+    # program holds both forms (vo_bench_stencil mode 0, then mode 1 = the fused form alone)
+    print("stencil alone ms: unfused", vo.bench_stencil(p, min(batch, frames_n), fused=False, reps=2), "fused", vo.bench_stencil(p, min(batch, frames_n), fused=True, reps=2))
     print("keypoints/frame", float(np.mean(nk)), "matches/pair", float(np.mean(nm)), "launches", vo.launch_count())
