@@ -9,7 +9,7 @@ import numpy as np
 _LIB = None
 _PKG = Path(__file__).resolve().parent
 
-SYMBOLS = ["vo_host_fundamental", "vo_host_normalize_points", "vo_host_score", "vo_host_sampson", "vo_host_ransac", "vo_host_get_pose", "vo_host_read_gt_line",
+SYMBOLS = ["vo_host_fundamental", "vo_host_normalize_points", "vo_host_score", "vo_host_triangulate", "vo_host_sampson", "vo_host_ransac", "vo_host_get_pose", "vo_host_read_gt_line",
            "vo_host_format_pose_csv", "vo_host_euler", "vo_host_read_gray", "vo_host_write_png", "vo_host_write_pgm",
            "vo_pipeline_run", "vo_pipeline_run_ex", "vo_host_last_error"]
 
@@ -104,6 +104,17 @@ def get_pose(F, p1, p2, gt_step=1.0, K=None):
     _ck(load_host_library().vo_host_get_pose(_dp(F), p1.ctypes.data_as(fp), p2.ctypes.data_as(fp), len(p1), C.c_double(gt_step), Kp,
                                              _dp(R), _dp(t), C.byref(votes)))
     return R.reshape(3, 3), t, votes.value
+
+
+def triangulate(R, t, n1, n2, force_scalar=False):
+    R = np.ascontiguousarray(R, np.float64).reshape(9)
+    t = np.ascontiguousarray(t, np.float64).reshape(3)
+    n1 = np.ascontiguousarray(n1, np.float32)
+    n2 = np.ascontiguousarray(n2, np.float32)
+    X = np.empty((len(n1), 4))
+    fp = C.POINTER(C.c_float)
+    _ck(load_host_library().vo_host_triangulate(_dp(R), _dp(t), n1.ctypes.data_as(fp), n2.ctypes.data_as(fp), len(n1), int(force_scalar), _dp(X)))
+    return X
 
 
 def read_gt_line(line):

@@ -59,6 +59,20 @@ int vo_host_normalize_points(const double* pts, int n, double* n1, double* n2, d
     });
 }
 
+int vo_host_triangulate(const double R[9], const double t[3], const float* n1, const float* n2, int n, int force_scalar, double* X) {
+    if (!R || !t || !n1 || !n2 || !X || n < 0) return fail(-1, "null argument");
+    return guarded([&] {
+        const vo::Mat3 r = to_mat3(R);
+        const vo::Vec3 tv{{t[0], t[1], t[2]}};
+        std::vector<vo::Point2f> a(n), b(n);
+        for (int i = 0; i < n; ++i) { a[i] = vo::Point2f{n1[2 * i], n1[2 * i + 1]}; b[i] = vo::Point2f{n2[2 * i], n2[2 * i + 1]}; }
+        double(*out)[4] = reinterpret_cast<double(*)[4]>(X);
+        if (force_scalar) for (int i = 0; i < n; ++i) vo::triangulatePoint(r, tv, a[i].x, a[i].y, b[i].x, b[i].y, out[i]);
+        else vo::triangulatePoints(r, tv, a.data(), b.data(), static_cast<size_t>(n), out);
+        return 0;
+    });
+}
+
 int vo_host_score(const double F[9], const double* pts, int n, double threshold, int force_scalar, uint8_t* flags, int* count) {
     if (!F || !pts || !flags || !count || n < 0) return fail(-1, "null argument");
     return guarded([&] {

@@ -1,12 +1,21 @@
 // vo_pose.cpp — see vo_pose.hpp.
 #include "vo_pose.hpp"
 
+#include <array>
 #include <cmath>
+#include <cstdlib>
+#include <limits>
+#include <vector>
 #include <cstdio>
 #include <fstream>
 #include <iomanip>
 #include <sstream>
 #include <stdexcept>
+
+#if defined(__x86_64__)
+#include <immintrin.h>
+#define VO_HAVE_AVX2_PATH 1
+#endif
 
 namespace vo {
 
@@ -151,6 +160,112 @@ void triangulatePoint(const Mat3& R, const Vec3& t, double x1, double y1, double
     for (int i = 0; i < 4; ++i) X[i] = V[i * 4 + 3];
 }
 
+#ifdef VO_HAVE_AVX2_PATH
+// triangulatePoint for four correspondences at once, one per AVX2 lane: the same operations in the same order, separate
+// multiplies and adds (no FMA), so every lane that converges returns bit for bit what the scalar routine returns.
+// Lanes whose Cholesky factor breaks down or whose inverse iteration has not converged after six steps are reported
+// in the returned mask and left to the scalar routine (which then takes its Jacobi fallback).
+__attribute__((target("avx2"))) static unsigned triangulate4(const Mat3& R, const Vec3& t, const double* x1, const double* y1, const double* x2,
+                                                             const double* y2, double X[4][4]) {
+    typedef __m256d V;
+#define S(v) _mm256_set1_pd(v)
+    const V vx1 = _mm256_loadu_pd(x1), vy1 = _mm256_loadu_pd(y1), vx2 = _mm256_loadu_pd(x2), vy2 = _mm256_loadu_pd(y2);
+    const double P1[3][4] = {{1, 0, 0, 0}, {0, 1, 0, 0}, {0, 0, 1, 0}};
+    double P2[3][4];
+    for (int i = 0; i < 3; ++i) { for (int j = 0; j < 3; ++j) P2[i][j] = R(i, j); P2[i][3] = t(i); }
+    V A[4][4];
+    for (int j = 0; j < 4; ++j) {
+        A[0][j] = _mm256_sub_pd(_mm256_mul_pd(vx1, S(P1[2][j])), S(P1[0][j]));
+        A[1][j] = _mm256_sub_pd(_mm256_mul_pd(vy1, S(P1[2][j])), S(P1[1][j]));
+        A[2][j] = _mm256_sub_pd(_mm256_mul_pd(vx2, S(P2[2][j])), S(P2[0][j]));
+        A[3][j] = _mm256_sub_pd(_mm256_mul_pd(vy2, S(P2[2][j])), S(P2[1][j]));
+    }
+    V M[4][4];
+    for (int i = 0; i < 4; ++i)
+        for (int j = i; j < 4; ++j) {
+            V acc = S(0.0);
+            for (int k = 0; k < 4; ++k) acc = _mm256_add_pd(acc, _mm256_mul_pd(A[k][i], A[k][j]));
+            M[i][j] = M[j][i] = acc;
+        }
+    const V shift = _mm256_mul_pd(S(1e-14), _mm256_add_pd(_mm256_add_pd(_mm256_add_pd(M[0][0], M[1][1]), M[2][2]), M[3][3]));
+    V ok = _mm256_cmp_pd(shift, S(0.0), _CMP_GT_OQ);
+    V L[4][4];
+    for (int i = 0; i < 4; ++i)
+        for (int j = 0; j <= i; ++j) {
+            V acc = i == j ? _mm256_add_pd(M[i][j], shift) : _mm256_add_pd(M[i][j], S(0.0));
+            for (int k = 0; k < j; ++k) acc = _mm256_sub_pd(acc, _mm256_mul_pd(L[i][k], L[j][k]));
+            if (i == j) { ok = _mm256_and_pd(ok, _mm256_cmp_pd(acc, S(0.0), _CMP_GT_OQ)); L[i][i] = _mm256_sqrt_pd(acc); }
+            else L[i][j] = _mm256_div_pd(acc, L[j][j]);
+        }
+    const V d[4] = {_mm256_div_pd(S(1.0), L[0][0]), _mm256_div_pd(S(1.0), L[1][1]), _mm256_div_pd(S(1.0), L[2][2]), _mm256_div_pd(S(1.0), L[3][3])};
+    V x[4] = {S(0.5), S(0.5), S(0.5), S(0.5)};
+    V active = ok, done = S(0.0);  // lane masks (all-ones / zero)
+    const V sign_bit = S(-0.0), inf = S(std::numeric_limits<double>::infinity());
+    for (int it = 0; it < 6; ++it) {
+        V y[4];
+        for (int i = 0; i < 4; ++i) {  // L z = x
+            V acc = x[i];
+            for (int k = 0; k < i; ++k) acc = _mm256_sub_pd(acc, _mm256_mul_pd(L[i][k], y[k]));
+            y[i] = _mm256_mul_pd(acc, d[i]);
+        }
+        for (int i = 3; i >= 0; --i) {  // L^T y = z
+            V acc = y[i];
+            for (int k = i + 1; k < 4; ++k) acc = _mm256_sub_pd(acc, _mm256_mul_pd(L[k][i], y[k]));
+            y[i] = _mm256_mul_pd(acc, d[i]);
+        }
+        const V nrm = _mm256_sqrt_pd(_mm256_add_pd(_mm256_add_pd(_mm256_add_pd(_mm256_mul_pd(y[0], y[0]), _mm256_mul_pd(y[1], y[1])),
+                                                                 _mm256_mul_pd(y[2], y[2])), _mm256_mul_pd(y[3], y[3])));
+        // nrm > 0 and finite, else the scalar routine breaks out (to its fallback): such lanes stop being active
+        const V good = _mm256_and_pd(_mm256_cmp_pd(nrm, S(0.0), _CMP_GT_OQ), _mm256_cmp_pd(nrm, inf, _CMP_LT_OQ));
+        active = _mm256_and_pd(active, good);
+        const V dotp = _mm256_add_pd(_mm256_add_pd(_mm256_add_pd(_mm256_mul_pd(y[0], x[0]), _mm256_mul_pd(y[1], x[1])), _mm256_mul_pd(y[2], x[2])),
+                                     _mm256_mul_pd(y[3], x[3]));
+        const V one = _mm256_blendv_pd(S(1.0), S(-1.0), _mm256_cmp_pd(dotp, S(0.0), _CMP_LT_OQ));
+        const V scale = _mm256_div_pd(one, nrm);
+        V change = S(0.0);
+        for (int i = 0; i < 4; ++i) {
+            const V v = _mm256_mul_pd(scale, y[i]);
+            change = _mm256_max_pd(change, _mm256_andnot_pd(sign_bit, _mm256_sub_pd(v, x[i])));
+            x[i] = _mm256_blendv_pd(x[i], v, active);  // lanes that are done (or broken) keep what they have
+        }
+        if (it > 0) {
+            const V conv = _mm256_and_pd(active, _mm256_cmp_pd(change, S(1e-11), _CMP_LT_OQ));
+            done = _mm256_or_pd(done, conv);
+            active = _mm256_andnot_pd(conv, active);
+        }
+        if (_mm256_movemask_pd(active) == 0) break;
+    }
+    double xs[4][4];
+    for (int i = 0; i < 4; ++i) _mm256_storeu_pd(xs[i], x[i]);
+    for (int lane = 0; lane < 4; ++lane)
+        for (int i = 0; i < 4; ++i) X[lane][i] = xs[i][lane];
+    return ~static_cast<unsigned>(_mm256_movemask_pd(done)) & 0xFu;  // lanes the scalar routine has to do
+#undef S
+}
+
+static bool pose_use_avx2() {
+    static const bool ok = __builtin_cpu_supports("avx2") && !std::getenv("VO_POSE_SCALAR");
+    return ok;
+}
+#endif
+
+// triangulatePoint over n correspondences (normalised float coordinates); X[i] = the unit null vector of point i
+void triangulatePoints(const Mat3& R, const Vec3& t, const Point2f* n1, const Point2f* n2, size_t n, double (*X)[4]) {
+    size_t i = 0;
+#ifdef VO_HAVE_AVX2_PATH
+    if (pose_use_avx2()) {
+        for (; i + 4 <= n; i += 4) {
+            double x1[4], y1[4], x2[4], y2[4];
+            for (int l = 0; l < 4; ++l) { x1[l] = n1[i + l].x; y1[l] = n1[i + l].y; x2[l] = n2[i + l].x; y2[l] = n2[i + l].y; }
+            const unsigned todo = triangulate4(R, t, x1, y1, x2, y2, X + i);
+            for (int l = 0; l < 4; ++l)
+                if (todo & (1u << l)) triangulatePoint(R, t, x1[l], y1[l], x2[l], y2[l], X[i + l]);
+        }
+    }
+#endif
+    for (; i < n; ++i) triangulatePoint(R, t, n1[i].x, n1[i].y, n2[i].x, n2[i].y, X[i]);
+}
+
 // PoseUpdate.hpp:61-179
 PoseResult PoseUpdate::getPoseEx(const Mat3& F, const std::vector<Point2f>& points1, const std::vector<Point2f>& points2,
                                  double GT_pos_norm) const {
@@ -195,13 +310,16 @@ PoseResult PoseUpdate::getPoseEx(const Mat3& F, const std::vector<Point2f>& poin
     //    can reach the leader's count even if every remaining point voted for it (its partial counts are then below the
     //    winner's and cannot be chosen).
     int positive[4] = {0, 0, 0, 0};
+    std::vector<std::array<double, 4>> scratch;
     auto vote = [&](int c, size_t i0, size_t i1) {  // candidates c = (R, +t) and c + 1 = (R, -t) over points [i0, i1)
         const Mat3& R = *Rs[c];
         const Vec3& tc = *ts[c];
+        std::vector<std::array<double, 4>>& XS = scratch;
+        XS.resize(i1 - i0);
+        triangulatePoints(R, tc, n1.data() + i0, n2.data() + i0, i1 - i0, reinterpret_cast<double(*)[4]>(XS.data()));
         for (size_t i = i0; i < i1; ++i) {
-            double X[4];
-            triangulatePoint(R, tc, n1[i].x, n1[i].y, n2[i].x, n2[i].y, X);
-            for (double& v : X) v = static_cast<double>(static_cast<float>(v));  // triangulatePoints returns CV_32F for float input
+            double* X = XS[i - i0].data();
+            for (int q = 0; q < 4; ++q) X[q] = static_cast<double>(static_cast<float>(X[q]));  // triangulatePoints returns CV_32F for float input
             const double w = X[3];
             if (std::fabs(w) < 1e-6) continue;
             const Vec3 P{{X[0] / w, X[1] / w, X[2] / w}};

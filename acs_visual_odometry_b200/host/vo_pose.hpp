@@ -58,5 +58,8 @@ public:
 // cv::triangulatePoints for one correspondence: the right singular vector of the smallest singular value
 // of the 4x4 DLT system built from P1 = [I | 0], P2 = [R | t] and normalised image points.
 void triangulatePoint(const Mat3& R, const Vec3& t, double x1, double y1, double x2, double y2, double X[4]);
+// The same for n correspondences; four at a time on AVX2 when the CPU has it (bit-identical to the scalar routine, which
+// also serves the lanes that do not converge; VO_POSE_SCALAR=1 in the environment forces the scalar loop).
+void triangulatePoints(const Mat3& R, const Vec3& t, const Point2f* n1, const Point2f* n2, size_t n, double (*X)[4]);
 
 }  // namespace vo

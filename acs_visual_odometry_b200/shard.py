@@ -37,7 +37,12 @@ def compose_shard_poses(shard_poses):
     shared boundary frame), in the CSV convention of VisualOdometry::run: line 0 is the start pose as it is, every
     later line is flipZ * T_curr (VisualOdometry.cpp:70,186).  Each shard starts from the identity; the only sequential
     step of the whole pipeline is the prefix product T_curr = T_curr * T_rel (VisualOdometry.cpp:184), applied here
-    once per shard: G_{s+1} = G_s * T_local_s(last).  Returns the list of poses of frames 0 .. n-1 in the same CSV
+    once per shard: G_{s+1} = G_s * T_local_s(last).
+    Restriction: every shard restarts the reference's "last valid frame" at its own first frame.  If the LAST pair of a
+    shard fails (fewer than 8 matches or inliers at the boundary frame), a sequential run would match the next frame
+    against the last valid frame before the boundary, the sharded run against the boundary frame itself, and the two
+    trajectories differ from there on (tools/pipeline_shard_bench.py counts such boundaries as boundary_pairs_failed).
+    Returns the list of poses of frames 0 .. n-1 in the same CSV
     convention (n = sum of shard lengths - (shards - 1))."""
     import numpy as np
     out, G = [], np.eye(4)

@@ -35,6 +35,10 @@ int vo_host_ransac(const double* pts, int n, double probability, double sampson_
  * p1 / p2: n x 2 floats (inlier pixel coordinates).  votes (may be NULL): cheirality count of the winner. */
 int vo_host_get_pose(const double F[9], const float* p1, const float* p2, int n, double gt_step, const double* K,
                      double R[9], double t[3], int* votes);
+/* cv::triangulatePoints as getPose uses it (PoseUpdate.hpp:114): P1 = [I | 0], P2 = [R | t], n1 / n2 = n x 2 normalised
+ * float coordinates; X receives n x 4 unit null vectors.  force_scalar 0: four points at a time on AVX2 when the CPU has
+ * it; 1: one at a time.  Both give the same bits. */
+int vo_host_triangulate(const double R[9], const double t[3], const float* n1, const float* n2, int n, int force_scalar, double* X);
 /* readGTLine (PoseUpdate.cpp:43-50) and one line of writePoseCSV (:52-69); buf receives a NUL-terminated line. */
 int vo_host_read_gt_line(const char* line, double T[16]);
 int vo_host_format_pose_csv(const double T[16], char* buf, int cap);

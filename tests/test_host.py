@@ -311,3 +311,26 @@ def test_vector_scoring_equals_scalar_and_sampson():
                 assert np.array_equal(fs.astype(bool), host.sampson(F, pts) < thr)
     # a zero model: every denominator is below 1e-12, every error "max" (ransac.cpp:21)
     assert host.score(np.zeros((3, 3)), scene(9, R, t), 1.0)[1] == 0
+
+
+def test_vector_triangulation_equals_scalar():
+    """getPose's cheirality test triangulates every inlier: the four-wide AVX2 routine must return the scalar routine's
+    bits, for well-conditioned points and for the ones that take the fallback (rays parallel to the baseline, points at
+    infinity, identical points)."""
+    rng = np.random.default_rng(12)
+    R, t = rot([0.1, 1, 0.2], 0.03), np.array([0.2, -0.05, 1.0])
+    t = t / np.linalg.norm(t)
+    Kinv = np.linalg.inv(K)
+    for n in (1, 3, 4, 5, 8, 203):
+        p = scene(n, R, t, seed=40 + n, noise=0.5)
+        n1 = (np.c_[p[:, :2], np.ones(n)] @ Kinv.T)[:, :2].astype(np.float32)
+        n2 = (np.c_[p[:, 2:], np.ones(n)] @ Kinv.T)[:, :2].astype(np.float32)
+        if n >= 8:  # degenerate lanes in the middle of a vector
+            n2[1] = n1[1]                          # no parallax
+            n1[2] = n2[2] = 0                      # on both optical axes
+            n2[5] = (n1[5] + 1e3).astype(np.float32)
+            n1[6] = np.float32(1e-30)
+        for Rm, tv in ((R, t), (R, -t), (np.eye(3), np.array([0, 0, 1.0])), (np.eye(3), np.zeros(3))):
+            a = host.triangulate(Rm, tv, n1, n2, force_scalar=False)
+            b = host.triangulate(Rm, tv, n1, n2, force_scalar=True)
+            assert np.array_equal(a.view(np.uint64), b.view(np.uint64)) or np.array_equal(np.isnan(a), np.isnan(b)) and np.array_equal(a[~np.isnan(a)], b[~np.isnan(b)])

@@ -90,6 +90,11 @@ def run_shard_pipeline(frames, fmt, batch, threads, out_path, rank, world, local
         "pairs_ok": sum(g["pairs_ok"] for g in gathered), "skipped_frames": sum(g["skipped_frames"] for g in gathered),
         "mean_inliers": float(np.mean([g["mean_inliers"] for g in gathered])),
         "per_rank_wall_s": [round(g["wall_s"], 3) for g in gathered],
+        # A shard whose LAST pair failed hands the next shard a boundary frame that the sequential run would not have
+        # used as its query frame (it keeps matching against the last valid frame, VisualOdometry.cpp:164-166, and that
+        # state does not cross shards): the stitched trajectory then differs from the 1-GPU one from that boundary on.
+        # A skipped frame repeats the previous pose, so it shows in the shard's own pose list.
+        "boundary_pairs_failed": sum(1 for g in gathered[:-1] if len(g["poses"]) >= 2 and np.allclose(g["poses"][-1], g["poses"][-2])),
     }
 
 
