@@ -2,6 +2,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <exception>
 #include <string>
 
@@ -30,6 +31,11 @@ int guarded(Fn fn) {
     catch (...) { return fail(-3, "unknown exception"); }
 }
 
+}  // namespace
+
+namespace {
+std::mutex g_ctx_mutex;
+vo::VisualOdometry::Context g_ctx;  // the context vo_pipeline_run built last (kept until the process ends or it is replaced)
 }  // namespace
 
 extern "C" {
@@ -189,6 +195,21 @@ int vo_pipeline_run_ex(int device, int num_threads, const char* image_dir, int n
         vo_.seed = seed;
         vo_.reuse_model = (flags & VO_PIPE_REUSE_MODEL) != 0;
         if (const char* e = std::getenv("VO_CAND_CAP")) vo_.cand_cap = std::atoi(e);  // tuning / test aid: candidates per frame
+        // the context of the previous call on this device is kept (one per process): a second sequence does not pay the
+        // device allocations again, like a long-lived VisualOdometry object
+        {
+            std::lock_guard<std::mutex> lk(g_ctx_mutex);
+            if (g_ctx.ctx && g_ctx.device == device) { vo_.adopt_context(g_ctx); g_ctx = vo::VisualOdometry::Context(); }
+        }
+        struct Keep {
+            vo::VisualOdometry& v;
+            ~Keep() {
+                vo::VisualOdometry::Context c = v.release_context();
+                std::lock_guard<std::mutex> lk(g_ctx_mutex);
+                if (g_ctx.ctx) vo_destroy(g_ctx.ctx);
+                g_ctx = c;
+            }
+        } keep{vo_};
         vo_.verbose = false;
         vo_.run(image_dir, static_cast<size_t>(num_images), pose_file, output_csv);
         const vo::RunStats& s = vo_.stats;

@@ -55,8 +55,25 @@ VisualOdometry::~VisualOdometry() {
     if (ctx_) vo_destroy(ctx_);
 }
 
+void VisualOdometry::adopt_context(const Context& c) {
+    if (!c.ctx) return;
+    if (ctx_ || c.device != device_ || c.max_keypoints != params.max_keypoints || c.batch != batch || c.cand_cap != cand_cap) {
+        vo_destroy(c.ctx);
+        return;
+    }
+    ctx_ = c.ctx; ctx_rows_ = c.rows; ctx_cols_ = c.cols; ctx_batch_ = c.batch; ctx_max_kp_ = c.max_keypoints;
+}
+
+VisualOdometry::Context VisualOdometry::release_context() {
+    Context c;
+    c.ctx = ctx_; c.rows = ctx_rows_; c.cols = ctx_cols_; c.max_keypoints = ctx_max_kp_; c.batch = ctx_batch_; c.cand_cap = cand_cap;
+    c.device = device_;
+    ctx_ = nullptr; ctx_rows_ = ctx_cols_ = 0;
+    return c;
+}
+
 void VisualOdometry::ensure_ctx(int rows, int cols) {
-    if (ctx_ && rows <= ctx_rows_ && cols <= ctx_cols_) return;
+    if (ctx_ && rows <= ctx_rows_ && cols <= ctx_cols_ && ctx_batch_ == batch && ctx_max_kp_ == params.max_keypoints) return;
     if (ctx_) { vo_destroy(ctx_); ctx_ = nullptr; }
     const int slots = 2 * (batch + 1) + 2;  // two chunk sets of batch+1 frames, plus two for on-demand pairs
     const int rc = vo_create_ex(&ctx_, device_, rows, cols, params.max_keypoints, slots, cand_cap);
@@ -65,7 +82,7 @@ void VisualOdometry::ensure_ctx(int rows, int cols) {
         ctx_ = nullptr;
         throw std::runtime_error("vo_create failed: " + msg);  // like the reference's "No OpenCL devices found" (VisualOdometry.cpp:18)
     }
-    ctx_rows_ = rows; ctx_cols_ = cols;
+    ctx_rows_ = rows; ctx_cols_ = cols; ctx_batch_ = batch; ctx_max_kp_ = params.max_keypoints;
 }
 
 // VisualOdometry.cpp:28-31

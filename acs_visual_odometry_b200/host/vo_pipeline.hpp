@@ -71,6 +71,12 @@ public:
     bool verbose = true;
     RunStats stats;
     const std::vector<Mat4>& poses() const { return estimated_poses_; }
+    // The GPU context is built on first use and lives as long as the object (the reference builds its OpenCL context in
+    // the constructor, VisualOdometry.cpp:9-25).  A caller that runs several sequences through short-lived objects (the C
+    // ABI's vo_pipeline_run) can hand a context over instead of paying the device allocations again.
+    struct Context { vo_ctx* ctx = nullptr; int rows = 0, cols = 0, max_keypoints = 0, batch = 0, cand_cap = 0, device = 0; };
+    void adopt_context(const Context& c);   // takes ownership if it fits this object's parameters, else destroys it
+    Context release_context();              // gives ownership away (ctx == nullptr if none was built)
 
 private:
     struct PairResult;
@@ -81,7 +87,7 @@ private:
     std::size_t number_of_threads_;
     int device_;
     vo_ctx* ctx_ = nullptr;
-    int ctx_rows_ = 0, ctx_cols_ = 0;
+    int ctx_rows_ = 0, ctx_cols_ = 0, ctx_batch_ = 0, ctx_max_kp_ = 0;
     std::vector<Mat4> estimated_poses_;
 };
 

@@ -483,7 +483,8 @@ def main():
         "ms_per_step_by_rank": [round(x, 4) for x in ms_ranks], "sm_mhz_by_rank": all_ranks(clocks.get("sm_mhz") or 0.0),
         "roofline": roofline, "roofline_unfused": unfused, "roofline_matcher": matcher if args.config != 2 else None,
         "kernel_ms_per_step": kernel_ms,
-        "keypoints_per_frame": float(np.mean(nk)), "matches_per_pair": float(np.mean(nm)) if len(nm) else 0.0,
+        "keypoints_per_frame": float(np.mean(nk)), "keypoints_per_frame_by_rank": [round(x, 1) for x in all_ranks(float(np.mean(nk)))],
+        "compares_per_rank": [round(x) for x in all_ranks(compares)], "matches_per_pair": float(np.mean(nm)) if len(nm) else 0.0,
         "compares_per_s": matcher["compares_per_s"] * world, "compares_per_s_note": "matcher kernel time only (x n_gpus)",
         "match_mode": "REF32" if args.match_bits == 32 else "FULL512",
     }

@@ -56,6 +56,8 @@ int vo_host_write_pgm(const char* path, const uint8_t* gray, int rows, int cols)
  * stats[16] (may be NULL): 0 frames, 1 pairs solved, 2 skipped frames, 3 missing frames, 4 re-matched pairs,
  * 5 wall s, 6 decode s, 7 front-end s, 8 RANSAC+pose s, 9 compose s, 10 RANSAC iterations, 11 mean keypoints,
  * 12 mean matches, 13 mean inliers. */
+/* The GPU context a call builds is kept for the next call on the same device with the same preset and batch (one per
+ * process), so a second sequence does not pay the device allocations again. */
 int vo_pipeline_run(int device, int num_threads, const char* image_dir, int num_images, const char* pose_file,
                     const char* output_csv, int preset, int batch, uint64_t seed, double* stats);
 /* The same with flags: VO_PIPE_REUSE_MODEL keeps one FundamentalMatrix across frames like the reference does
