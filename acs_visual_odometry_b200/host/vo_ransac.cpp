@@ -67,6 +67,43 @@ __attribute__((target("avx2"))) int score_avx2(const double* F, const double* X0
 }
 #endif
 
+#ifdef VO_HAVE_AVX2_PATH
+// the same loop eight correspondences at a time
+__attribute__((target("avx512f"))) int score_avx512(const double* F, const double* X0, const double* X1, const double* P0, const double* P1,
+                                                    int n, double thr, unsigned char* flag) {
+    const __m512d f00 = _mm512_set1_pd(F[0]), f01 = _mm512_set1_pd(F[1]), f02 = _mm512_set1_pd(F[2]), f10 = _mm512_set1_pd(F[3]),
+                  f11 = _mm512_set1_pd(F[4]), f12 = _mm512_set1_pd(F[5]), f20 = _mm512_set1_pd(F[6]), f21 = _mm512_set1_pd(F[7]),
+                  f22 = _mm512_set1_pd(F[8]);
+    const __m512d eps = _mm512_set1_pd(1e-12), vthr = _mm512_set1_pd(thr);
+    int count = 0, i = 0;
+    for (; i + 8 <= n; i += 8) {
+        const __m512d x0 = _mm512_loadu_pd(X0 + i), x1 = _mm512_loadu_pd(X1 + i), p0 = _mm512_loadu_pd(P0 + i), p1 = _mm512_loadu_pd(P1 + i);
+        const __m512d Fx0 = _mm512_add_pd(_mm512_add_pd(_mm512_mul_pd(f00, x0), _mm512_mul_pd(f01, x1)), f02);
+        const __m512d Fx1 = _mm512_add_pd(_mm512_add_pd(_mm512_mul_pd(f10, x0), _mm512_mul_pd(f11, x1)), f12);
+        const __m512d Fx2 = _mm512_add_pd(_mm512_add_pd(_mm512_mul_pd(f20, x0), _mm512_mul_pd(f21, x1)), f22);
+        const __m512d Ft0 = _mm512_add_pd(_mm512_add_pd(_mm512_mul_pd(f00, p0), _mm512_mul_pd(f10, p1)), f20);
+        const __m512d Ft1 = _mm512_add_pd(_mm512_add_pd(_mm512_mul_pd(f01, p0), _mm512_mul_pd(f11, p1)), f21);
+        const __m512d e = _mm512_add_pd(_mm512_add_pd(_mm512_mul_pd(p0, Fx0), _mm512_mul_pd(p1, Fx1)), Fx2);
+        const __m512d den = _mm512_add_pd(_mm512_add_pd(_mm512_add_pd(_mm512_mul_pd(Fx0, Fx0), _mm512_mul_pd(Fx1, Fx1)), _mm512_mul_pd(Ft0, Ft0)),
+                                          _mm512_mul_pd(Ft1, Ft1));
+        const __m512d err = _mm512_div_pd(_mm512_mul_pd(e, e), den);
+        const unsigned m = static_cast<unsigned>(_mm512_cmp_pd_mask(den, eps, _CMP_GE_OQ) & _mm512_cmp_pd_mask(err, vthr, _CMP_LT_OQ));
+        for (int b = 0; b < 8; ++b) flag[i + b] = (m >> b) & 1u;
+        count += __builtin_popcount(m);
+    }
+    return count + score_scalar(F, X0, X1, P0, P1, i, n, thr, flag);
+}
+#endif
+
+bool use_avx512() {
+#ifdef VO_HAVE_AVX2_PATH
+    static const bool ok = __builtin_cpu_supports("avx512f") && !std::getenv("VO_RANSAC_SCALAR") && !std::getenv("VO_RANSAC_NO_AVX512");
+    return ok;
+#else
+    return false;
+#endif
+}
+
 bool use_avx2() {
 #ifdef VO_HAVE_AVX2_PATH
     static const bool ok = __builtin_cpu_supports("avx2") && !std::getenv("VO_RANSAC_SCALAR");
@@ -82,6 +119,7 @@ bool use_avx2() {
 int score_correspondences(const double F[9], const double* X0, const double* X1, const double* P0, const double* P1, int n, double thr,
                           unsigned char* flag, bool force_scalar) {
 #ifdef VO_HAVE_AVX2_PATH
+    if (!force_scalar && use_avx512()) return score_avx512(F, X0, X1, P0, P1, n, thr, flag);
     if (!force_scalar && use_avx2()) return score_avx2(F, X0, X1, P0, P1, n, thr, flag);
 #endif
     return score_scalar(F, X0, X1, P0, P1, 0, n, thr, flag);
