@@ -8,6 +8,8 @@
 
 #include <algorithm>
 
+#include <nvtx3/nvToolsExt.h>
+
 #include "vo_internal.cuh"
 
 namespace {
@@ -29,14 +31,25 @@ int fail_cuda(vo_ctx* c, cudaError_t e, const char* what) {
     } while (0)
 
 // kernel launch with launch counting and optional per-family event timing
+// NVTX ranges around every launch, named by kernel family, when VO_NVTX is set in the environment (header-only NVTX3:
+// nothing links; a tool that understands NVTX - ncu --nvtx --nvtx-include "stencil/" - can then select a family).
+static const char* const kFamilyNames[] = {"stencil", "nms", "select", "freak", "match", "finalize", "misc", "other"};
+static bool nvtx_on() {
+    static const bool on = getenv("VO_NVTX") != nullptr;
+    return on;
+}
+
 #define RUN(c, fam, expr)                                            \
     do {                                                             \
         ProfRec pr_{(fam), nullptr, nullptr};                        \
+        const bool nvtx_ = nvtx_on();                                \
+        if (nvtx_) nvtxRangePushA(kFamilyNames[(fam) & 7]);          \
         if ((c)->profiling) {                                        \
             cudaEventCreate(&pr_.a); cudaEventCreate(&pr_.b);        \
             cudaEventRecord(pr_.a, (c)->s_cur);                  \
         }                                                            \
         cudaError_t e_ = (expr);                                     \
+        if (nvtx_) nvtxRangePop();                                   \
         if ((c)->profiling) {                                        \
             cudaEventRecord(pr_.b, (c)->s_cur);                  \
             (c)->prof.push_back(pr_);                                \
@@ -98,6 +111,10 @@ int run_extract(vo_ctx* c, const uint8_t* in_base, size_t in_fstride, size_t in_
     sa.response = p->response; sa.harris_k = p->harris_k;
     sa.nms_h = fused ? p->nms_window / 2 : 0;
     sa.cand = c->d_cand + so * c->cand_cap; sa.cand_cap = c->cand_cap; sa.cand_count = c->d_cand_count + so;
+    if (c->stencil_cap > 0) {
+        sa.task_counter = c->d_task_counter + (c->task_counter_next++ & 7); sa.ctas_per_sm_cap = c->stencil_cap;
+        CK(c, cudaMemsetAsync(sa.task_counter, 0, sizeof(int), c->s_cur));
+    }
     RUN(c, FAM_STENCIL, launch_stencil(sa, n, from_blurred ? STENCIL_SRC_BLURRED : STENCIL_SRC_GRAY, c->s_cur));
     for (int k = 0; k < n; ++k) {
         c->slot_rows[first_slot + k] = rows; c->slot_cols[first_slot + k] = cols;
@@ -299,6 +316,8 @@ int vo_create_ex(vo_ctx** out, int device, int max_rows, int max_cols, int max_k
     CKC(cudaMemset(c->d_nkp, 0, ts * sizeof(int)));
     CKC(cudaMemset(c->d_flags, 0, ts * sizeof(int)));
     CKC(cudaMemset(c->d_cand_count, 0, ts * sizeof(int)));
+    CKC(cudaMalloc(&c->d_task_counter, 8 * sizeof(int)));
+    if (const char* e = getenv("VO_STENCIL_CAP")) c->stencil_cap = atoi(e);  // tuning: persistent stencil CTAs per SM (0 = one CTA per task)
     CKC(cudaMallocHost(&c->h_small, sizeof(int) * 4 * (2 * VO_MAX_BATCH + 8)));
     c->slot_rows = new int[c->total_slots]();
     c->slot_cols = new int[c->total_slots]();
@@ -332,7 +351,7 @@ void vo_destroy(vo_ctx* c) {
     if (c->s_h2d) cudaStreamSynchronize(c->s_h2d);
     if (c->s_d2h) cudaStreamSynchronize(c->s_d2h);
     for (auto& r : c->prof) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
-    cudaFree(c->d_img); cudaFree(c->d_blur); cudaFree(c->d_R); cudaFree(c->d_cand); cudaFree(c->d_cand_count);
+    cudaFree(c->d_img); cudaFree(c->d_blur); cudaFree(c->d_R); cudaFree(c->d_cand); cudaFree(c->d_cand_count); cudaFree(c->d_task_counter);
     cudaFree(c->d_kp); cudaFree(c->d_desc); cudaFree(c->d_angles); cudaFree(c->d_nkp); cudaFree(c->d_flags);
     cudaFree(c->d_partial); cudaFree(c->d_raw); cudaFree(c->d_pairs); cudaFree(c->d_nmatch); cudaFree(c->d_bytes);
     cudaFree(c->d_seq); cudaFree(c->d_seq_nkp); cudaFree(c->d_seq_kp); cudaFree(c->d_seq_nmatch); cudaFree(c->d_seq_pairs);
@@ -950,6 +969,10 @@ int vo_bench_stencil(vo_ctx* c, const vo_params* p, int batch, int mode, int rep
     float total = 0.f;
     for (int r = 0; r < reps; ++r) {
         CK(c, cudaMemsetAsync(c->d_cand_count, 0, sizeof(int) * batch, c->s_compute));
+        if (c->stencil_cap > 0) {
+            sa.task_counter = c->d_task_counter + (c->task_counter_next++ & 7); sa.ctas_per_sm_cap = c->stencil_cap;
+            CK(c, cudaMemsetAsync(sa.task_counter, 0, sizeof(int), c->s_compute));
+        }
         CK(c, cudaEventRecord(c->ev_t0, c->s_compute));
         cudaError_t e = launch_stencil(sa, batch, STENCIL_SRC_GRAY, c->s_compute);
         c->launches++;

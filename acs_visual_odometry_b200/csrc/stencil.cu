@@ -41,6 +41,7 @@
 // result (FMAs by the exact constants -1 / 4 / 0.5, sums, the sqrt refinement's intended FMAs).
 #include <cuda_fp16.h>
 
+#include <algorithm>
 #include <cstdlib>
 #include <type_traits>
 
@@ -241,9 +242,15 @@ k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows, int n_tas
     __shared__ __align__(16) char s_rings[NWARP][FUSED ? RING_BYTES_FUSED : RING_BYTES];
     const int lane = threadIdx.x & 31;
     // tasks = (frame, row segment, strip), numbered across the whole batch so that no warp slot of a CTA idles
-    const int gtask = blockIdx.x * NWARP + (threadIdx.x >> 5);
-    if (gtask >= n_tasks) return;  // whole warp
     char* const ring = s_rings[threadIdx.x >> 5];
+    int gtask = blockIdx.x * NWARP + (threadIdx.x >> 5);
+    for (;;) {  // one task per warp, or - persistent form - tasks from a counter until none is left
+    if (a.task_counter) {
+        int t = 0;
+        if (lane == 0) t = atomicAdd(a.task_counter, 1);
+        gtask = __shfl_sync(FULL, t, 0);
+    }
+    if (gtask >= n_tasks) return;  // whole warp
     const int per_frame = n_strips * n_segs;
     const int f = gtask / per_frame, task = gtask - f * per_frame;
     const int strip = task % n_strips, seg = task / n_strips;
@@ -671,6 +678,9 @@ k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows, int n_tas
         }
     }
     if (FUSED) flush_candidates();
+    if (!a.task_counter) return;
+    __syncwarp();
+    }  // next task
 }
 
 // custom_bgr2gray: saturate_cast<uchar>(0.114*B + 0.587*G + 0.299*R) in double, round-half-even
@@ -737,7 +747,9 @@ cudaError_t launch_stencil(const StencilArgs& a, int n_frames, int src, cudaStre
     const int n_segs = (a.rows + seg_rows - 1) / seg_rows;
     const long long n_tasks = (long long)n_strips * n_segs * n_frames;
     if (n_tasks > 0x7FFFFFFFll) return cudaErrorInvalidValue;
-    const dim3 grid((unsigned)((n_tasks + NWARP - 1) / NWARP));
+    long long n_ctas = (n_tasks + NWARP - 1) / NWARP;
+    if (a.task_counter && a.ctas_per_sm_cap > 0) n_ctas = std::min<long long>(n_ctas, (long long)a.ctas_per_sm_cap * sm_count_cached());
+    const dim3 grid((unsigned)n_ctas);
     const bool gather = a.cols < 16 || a.rows < 8;
     const bool aligned = ((reinterpret_cast<uintptr_t>(a.in) | a.in_pitch | a.in_fstride) & 3) == 0;
 #define VO_LAUNCH(SR, GA, AL, NH) k_stencil<SR, GA, AL, NH><<<grid, 32 * NWARP, 0, st>>>(a, n_strips, n_segs, seg_rows, (int)n_tasks)

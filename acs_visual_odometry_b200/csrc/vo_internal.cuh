@@ -30,6 +30,7 @@ struct vo_ctx {
     float* d_R = nullptr;        // [total_slots][max_rows][r_pitch]    thresholded response; allocated on first use (ensure_R)
     unsigned long long* d_cand = nullptr;  // [total_slots][cand_cap]   (Rbits<<32 | i<<16 | j)
     int* d_cand_count = nullptr; // [total_slots]
+    int* d_task_counter = nullptr; int task_counter_next = 0, stencil_cap = 0;  // persistent stencil form (VO_STENCIL_CAP)
     float2* d_kp = nullptr;      // [total_slots][max_kp]               (x, y)
     uint32_t* d_desc = nullptr;  // [total_slots][max_kp][16]           packed descriptors
     float* d_angles = nullptr;   // [total_slots][max_kp]
@@ -87,6 +88,9 @@ struct StencilArgs {
     float* R; size_t R_fstride, R_pitch;                // floats; unused (may be null) when nms_h > 0
     int rows, cols; float threshold;
     int response = 0; float harris_k = 0.f;             // VO_RESPONSE_*; HARRIS only with nms_h == 0
+    // persistent form (tuning, VO_STENCIL_CAP): ctas_per_sm_cap x SMs single-warp CTAs fetch tasks from *task_counter
+    // (zeroed by the caller) instead of one CTA per task, so that the kernel leaves room on every SM for other kernels
+    int* task_counter = nullptr; int ctas_per_sm_cap = 0;
     // fused non-maximum suppression: half window 1 or 2 (0 = write R instead); candidates are appended to
     // cand[frame * cand_cap ...] with cand_count[frame] (zeroed by the caller) exactly as k_nms does
     int nms_h; unsigned long long* cand; int cand_cap; int* cand_count;
