@@ -595,3 +595,17 @@ def test_stage_workers_with_intervals(vo_small, oracle, factory):
     # custom_bgr2gray
     bgr = rng.integers(0, 256, (50, 70, 3), dtype=np.uint8)
     assert np.array_equal(vo_small.bgr2gray(bgr), oracle.bgr2gray(bgr))
+
+
+def test_describe_every_partial_cta(vo_small, oracle, factory):
+    """k_freak gives every thread two keypoints (q and q + 128 of a 256-keypoint CTA): counts around the half and the
+    full CTA exercise threads without a second keypoint, CTAs with a single thread, and the last partly filled CTA."""
+    blurred = oracle.blur(factory[0])
+    kp_all, _ = oracle.extract(factory[0], 25000.0, 5, 1500)
+    assert len(kp_all) > 600
+    for n in (1, 2, 3, 127, 128, 129, 255, 256, 257, 383, 385, 513):
+        kp = kp_all[:n]
+        d_o, a_o = oracle.describe(blurred, kp)
+        d_g, a_g = vo_small.describe(blurred, kp)
+        assert d_g.shape == d_o.shape and (d_g == d_o).mean() >= DESC_AGREEMENT_MIN, n
+        assert np.max(np.abs(a_g - a_o)) <= ANGLE_ATOL, n
