@@ -6,6 +6,7 @@
 #include <cstdio>
 #include <cstring>
 #include <future>
+#include <mutex>
 #include <stdexcept>
 #include <thread>
 
@@ -28,6 +29,39 @@ void parallel_for(size_t n, size_t threads, Fn fn) {
     for (size_t t = 0; t < threads; ++t)
         pool.emplace_back([&] { for (size_t i = next++; i < n; i = next++) fn(i); });
     for (auto& th : pool) th.join();
+}
+
+// Page-locked staging buffers are expensive to create (the driver pins every page) and a run needs about 100 MB of
+// them: they are kept in a process-wide pool between runs, like the GPU context (a second sequence through
+// vo_pipeline_run pays neither again).  Never returned to the driver before the process ends.
+struct PinnedPool {
+    std::mutex m;
+    std::vector<std::pair<void*, size_t>> free_blocks;
+    void* acquire(size_t bytes, size_t* got) {
+        {
+            std::lock_guard<std::mutex> lk(m);
+            size_t best = free_blocks.size();  // best fit: the smallest block that is large enough
+            for (size_t i = 0; i < free_blocks.size(); ++i)
+                if (free_blocks[i].second >= bytes && (best == free_blocks.size() || free_blocks[i].second < free_blocks[best].second)) best = i;
+            if (best < free_blocks.size()) {
+                void* p = free_blocks[best].first;
+                *got = free_blocks[best].second;
+                free_blocks.erase(free_blocks.begin() + best);
+                return p;
+            }
+        }
+        *got = bytes;
+        return vo_host_alloc(bytes);
+    }
+    void release(void* p, size_t bytes) {
+        if (!p) return;
+        std::lock_guard<std::mutex> lk(m);
+        free_blocks.emplace_back(p, bytes);
+    }
+};
+PinnedPool& pinned_pool() {
+    static PinnedPool* pool = new PinnedPool();  // leaked on purpose: no destruction-order games with the CUDA runtime at exit
+    return *pool;
 }
 
 void check(vo_ctx* ctx, int rc, const char* what) {
@@ -175,6 +209,7 @@ struct Chunk {
     // overlap the next chunk's kernels only into page-locked memory
     int32_t* nkp = nullptr; int32_t* nmatch = nullptr; int32_t* pairs = nullptr;
     float* kp = nullptr;
+    size_t cap[5] = {0, 0, 0, 0, 0};  // pool capacities of pixels, nkp, nmatch, kp, pairs
     double decode_s = 0;
 };
 
@@ -207,15 +242,19 @@ void VisualOdometry::run(const std::string image_dir, const size_t num_images, c
 
     Chunk chunks[3];
     auto free_chunks = [&] {
-        for (Chunk& c : chunks) { vo_host_free(c.pixels); vo_host_free(c.nkp); vo_host_free(c.nmatch); vo_host_free(c.pairs); vo_host_free(c.kp); }
+        for (Chunk& c : chunks) {
+            pinned_pool().release(c.pixels, c.cap[0]); pinned_pool().release(c.nkp, c.cap[1]); pinned_pool().release(c.nmatch, c.cap[2]);
+            pinned_pool().release(c.kp, c.cap[3]); pinned_pool().release(c.pairs, c.cap[4]);
+            c.pixels = nullptr; c.nkp = c.nmatch = c.pairs = nullptr; c.kp = nullptr;
+        }
     };
     for (Chunk& c : chunks) {
         const size_t nf = static_cast<size_t>(batch) + 1;
-        c.pixels = static_cast<uint8_t*>(vo_host_alloc(fbytes * nf));
-        c.nkp = static_cast<int32_t*>(vo_host_alloc(sizeof(int32_t) * nf));
-        c.nmatch = static_cast<int32_t*>(vo_host_alloc(sizeof(int32_t) * nf));
-        c.kp = static_cast<float*>(vo_host_alloc(sizeof(float) * nf * maxkp * 2));
-        c.pairs = static_cast<int32_t*>(vo_host_alloc(sizeof(int32_t) * nf * maxkp * 2));
+        c.pixels = static_cast<uint8_t*>(pinned_pool().acquire(fbytes * nf, &c.cap[0]));
+        c.nkp = static_cast<int32_t*>(pinned_pool().acquire(sizeof(int32_t) * nf, &c.cap[1]));
+        c.nmatch = static_cast<int32_t*>(pinned_pool().acquire(sizeof(int32_t) * nf, &c.cap[2]));
+        c.kp = static_cast<float*>(pinned_pool().acquire(sizeof(float) * nf * maxkp * 2, &c.cap[3]));
+        c.pairs = static_cast<int32_t*>(pinned_pool().acquire(sizeof(int32_t) * nf * maxkp * 2, &c.cap[4]));
         if (!c.pixels || !c.nkp || !c.nmatch || !c.kp || !c.pairs) { free_chunks(); throw std::runtime_error("vo_host_alloc failed"); }
     }
     std::vector<uint8_t> anchor(fbytes);  // pixels of the query frame while a failure streak lasts
