@@ -94,3 +94,51 @@ def test_shard_pose_composition_equals_the_unsharded_trajectory():
         got = compose_shard_poses(shards)
         assert len(got) == n
         assert max(np.abs(g - w).max() for g, w in zip(got, whole)) < 1e-12
+
+
+def test_failed_boundary_pair_is_the_stated_limit_of_sharding():
+    """The reference advances its query frame only on success (VisualOdometry.cpp:164-166) and that state does not cross
+    shard boundaries.  With the sequential frame-loop oracle on scripted stages: when the pair that ENDS a shard
+    succeeds, the stitched shards equal the sequential run; when it fails, the next shard starts from a frame the
+    sequential run never uses as its query and the trajectories part at the boundary (shard.py states the restriction,
+    tools/pipeline_shard_bench.py counts such boundaries)."""
+    from acs_visual_odometry_b200.shard import compose_shard_poses, shard_frames
+    from oracle.vo_loop_oracle import run_loop
+    n = 13
+    gt = np.zeros((n, 3, 4))
+    gt[:, :, :3] = np.eye(3)
+    gt[:, 2, 3] = np.arange(n) * 2.0
+
+    def run(lo, hi, bad):  # frames lo..hi inclusive as one driver would process them; `bad` frames have no features
+        frames = [np.full((2, 2), i, np.uint8) for i in range(lo, hi + 1)]
+
+        def extract(img):
+            i = int(img[0, 0])
+            return np.c_[np.arange(32, dtype=np.float32) + i, np.arange(32, dtype=np.float32)], i
+
+        def match(d1, d2):
+            m = 0 if d2 in bad else 20
+            return np.c_[np.arange(m), np.arange(m)].astype(np.int32)
+
+        def ransac(pts, i):
+            return np.eye(3), pts
+
+        def get_pose(F, p1, p2, s):  # the step depends on WHICH query frame the pair started from
+            th = 0.01 * float(p1[0, 0])
+            R = np.array([[np.cos(th), 0, np.sin(th)], [0, 1, 0], [-np.sin(th), 0, np.cos(th)]])
+            return R, np.array([0, 0, s])
+
+        return list(run_loop(frames, gt[lo:hi + 1], extract, match, ransac, get_pose)[0])
+
+    lo1, hi1 = shard_frames(n, 0, 2)
+    lo2, hi2 = shard_frames(n, 1, 2)
+    boundary = hi1 - 1
+    assert lo2 == boundary
+    for bad, same in (({3}, True), ({boundary}, False)):
+        whole = run(0, n - 1, bad)
+        stitched = compose_shard_poses([run(lo1, hi1 - 1, bad), run(lo2, hi2 - 1, bad)])
+        assert len(stitched) == n
+        diff = max(np.abs(a - b).max() for a, b in zip(stitched, whole))
+        assert (diff < 1e-12) == same, (bad, diff)
+        if not same:  # identical up to the boundary frame, different after it
+            assert max(np.abs(a - b).max() for a, b in zip(stitched[:boundary + 1], whole[:boundary + 1])) < 1e-12
