@@ -66,7 +66,61 @@ __device__ __forceinline__ u64 add2(u64 a, u64 b) { u64 d; asm("add.rn.f32x2 %0,
 __device__ __forceinline__ u64 sub2(u64 a, u64 b) { u64 d; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
 __device__ __forceinline__ u64 f2_as_u64(float2 v) { return pk(v.x, v.y); }
 
-__global__ void __launch_bounds__(FK_NT, VO_FK_MINB) k_freak(const FreakArgs a) {
+#ifndef VO_FK_SPLIT
+#define VO_FK_SPLIT 0
+#endif
+#ifndef VO_FK_MINB_ORIENT
+#define VO_FK_MINB_ORIENT 8
+#endif
+#ifndef VO_FK_MINB_DESCRIBE
+#define VO_FK_MINB_DESCRIBE 5
+#endif
+
+// Rotated samples and the 512 tests of one keypoint (FREAK_feature_descriptor_parallel.cpp:110-151), given its angle.
+__device__ __forceinline__ void describe_keypoint(const FreakArgs& a, int f, int q, float2 kp, float angle, const uint8_t* __restrict__ img, int pitch) {
+    const float cs = (float)cos((double)angle), sn = (float)sin((double)angle);
+    // rotated samples: rm = {cos, -sin, sin, cos}; x' = (int)(kx + px*rm0 + py*rm2); y' = (int)(ky + (-1)*px*rm1 + py*rm3)
+    // (-1)*px*rm1 = (-px)*(-sin) = RN(px*sin) exactly, so the products below are the reference's.
+    int v[VO_FREAK_POINTS];
+#define VO_SAMPLE(i, PX, PY)                                                                             \
+    {                                                                                                    \
+        const float fx = __fadd_rn(__fadd_rn(kp.x, __fmul_rn((float)(PX), cs)), __fmul_rn((float)(PY), sn)); \
+        const float fy = __fadd_rn(__fadd_rn(kp.y, __fmul_rn((float)(PX), sn)), __fmul_rn((float)(PY), cs)); \
+        v[i] = img[(int)fy * pitch + (int)fx]; /* truncation toward zero */                               \
+    }
+    VO_FREAK_POINT_LIST(VO_SAMPLE)
+#undef VO_SAMPLE
+    // test j: bit = v[A] > v[B] = sign of v[B] - v[A]; one subtract and one funnel shift push it into the word
+    // (first test ends up in bit 31: the word is bit-reversed once at the end)
+    uint32_t w[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) w[i] = 0u;
+#define VO_TEST(j, A, B) w[(j) >> 5] = __funnelshift_l(static_cast<uint32_t>(v[B] - v[A]), w[(j) >> 5], 1);
+    VO_FREAK_TEST_LIST(VO_TEST)
+#undef VO_TEST
+#pragma unroll
+    for (int i = 0; i < 16; ++i) w[i] = __brev(w[i]);
+    uint4* __restrict__ out = reinterpret_cast<uint4*>(a.desc + ((size_t)f * a.kp_stride + q) * 16);
+    out[0] = make_uint4(w[0], w[1], w[2], w[3]);
+    out[1] = make_uint4(w[4], w[5], w[6], w[7]);
+    out[2] = make_uint4(w[8], w[9], w[10], w[11]);
+    out[3] = make_uint4(w[12], w[13], w[14], w[15]);
+}
+
+// Split form (VO_FK_SPLIT=1, off): the descriptor half as its own kernel, one keypoint per thread, reading the angles the
+// orientation kernel wrote - the orientation loop then runs at 64 registers and 32 warps per SM instead of 119 and 16.
+// Measured (profiles/r02E_variants_freak_split.jsonl): 1.07 ms per 1000 KITTI frames against 0.648 ms for the single
+// kernel, identical outputs - the descriptor phase hides behind other warps' orientation loops in the single kernel and
+// is exposed on its own.  Kept as a build option only.
+__global__ void __launch_bounds__(FK_NT, VO_FK_MINB_DESCRIBE) k_describe(const FreakArgs a) {
+    const int f = blockIdx.y, q = blockIdx.x * FK_NT + threadIdx.x;
+    if (q >= a.nkp[f]) return;
+    describe_keypoint(a, f, q, a.kp[(size_t)f * a.kp_stride + q], a.angles[(size_t)f * a.kp_stride + q], a.blur + (size_t)f * a.blur_fstride,
+                      (int)a.blur_pitch);
+}
+
+template <bool SPLIT>
+__global__ void __launch_bounds__(FK_NT, SPLIT ? VO_FK_MINB_ORIENT : VO_FK_MINB) k_freak(const FreakArgs a) {
     // Unrotated samples in shared memory, per thread (one conflict-free vector row per warp access):
     //   s_p[p]   = sample p of keypoint 0 (low byte) and of keypoint 1 (high byte);
     //   s_win[w] = the six samples 1+6w .. 6+6w of keypoint 0 (bytes 0-5 of .x/.y) and of keypoint 1 (.z/.w).
@@ -95,18 +149,23 @@ __global__ void __launch_bounds__(FK_NT, VO_FK_MINB) k_freak(const FreakArgs a) 
     {
         const uint8_t* __restrict__ c0 = img + (size_t)(int)kp0.y * a.blur_pitch + (int)kp0.x;
         const uint8_t* __restrict__ c1 = img + (size_t)(int)kp1.y * a.blur_pitch + (int)kp1.x;
-        uint32_t b0[VO_FREAK_POINTS], b1[VO_FREAK_POINTS];
-#pragma unroll
-        for (int p = 0; p < VO_FREAK_POINTS; ++p) {
-            const int off = (int)c_py[p] * pitch + (int)c_px[p];
-            b0[p] = c0[off]; b1[p] = c1[off];
-            s_p[p][t] = (unsigned short)(b0[p] | (b1[p] << 8));
+        {
+            const int off = (int)c_py[0] * pitch + (int)c_px[0];
+            s_p[0][t] = (unsigned short)((uint32_t)c0[off] | ((uint32_t)c1[off] << 8));
         }
 #pragma unroll
-        for (int w = 0; w < FK_WINDOWS; ++w) {
-            const int r = 1 + FK_GROUP * w;
-            s_win[w][t] = make_uint4(b0[r] | (b0[r + 1] << 8) | (b0[r + 2] << 16) | (b0[r + 3] << 24), b0[r + 4] | (b0[r + 5] << 8),
-                                     b1[r] | (b1[r + 1] << 8) | (b1[r + 2] << 16) | (b1[r + 3] << 24), b1[r + 4] | (b1[r + 5] << 8));
+        for (int w = 0; w < FK_WINDOWS; ++w) {  // window by window: at most twelve samples live at a time
+            uint32_t lo0 = 0, hi0 = 0, lo1 = 0, hi1 = 0;
+#pragma unroll
+            for (int i = 0; i < FK_GROUP; ++i) {
+                const int p = 1 + FK_GROUP * w + i;
+                const int off = (int)c_py[p] * pitch + (int)c_px[p];
+                const uint32_t x0 = c0[off], x1 = c1[off];
+                s_p[p][t] = (unsigned short)(x0 | (x1 << 8));
+                if (i < 4) { lo0 |= x0 << (8 * i); lo1 |= x1 << (8 * i); }
+                else { hi0 |= x0 << (8 * (i - 4)); hi1 |= x1 << (8 * (i - 4)); }
+            }
+            s_win[w][t] = make_uint4(lo0, hi0, lo1, hi1);
         }
     }
 
@@ -164,34 +223,7 @@ __global__ void __launch_bounds__(FK_NT, VO_FK_MINB) k_freak(const FreakArgs a) 
         float angle = 0.0f;
         if (!(isnan(ox) || isnan(oy))) angle = (float)atan2((double)oy, (double)ox);
         a.angles[(size_t)f * a.kp_stride + q] = angle;
-        const float cs = (float)cos((double)angle), sn = (float)sin((double)angle);
-
-        // rotated samples: rm = {cos, -sin, sin, cos}; x' = (int)(kx + px*rm0 + py*rm2); y' = (int)(ky + (-1)*px*rm1 + py*rm3)
-        // (-1)*px*rm1 = (-px)*(-sin) = RN(px*sin) exactly, so the products below are the reference's.
-        int v[VO_FREAK_POINTS];
-#define VO_SAMPLE(i, PX, PY)                                                                             \
-    {                                                                                                    \
-        const float fx = __fadd_rn(__fadd_rn(kp.x, __fmul_rn((float)(PX), cs)), __fmul_rn((float)(PY), sn)); \
-        const float fy = __fadd_rn(__fadd_rn(kp.y, __fmul_rn((float)(PX), sn)), __fmul_rn((float)(PY), cs)); \
-        v[i] = img[(int)fy * pitch + (int)fx]; /* truncation toward zero */                               \
-    }
-        VO_FREAK_POINT_LIST(VO_SAMPLE)
-#undef VO_SAMPLE
-        // test j: bit = v[A] > v[B] = sign of v[B] - v[A]; one subtract and one funnel shift push it into the word
-        // (first test ends up in bit 31: the word is bit-reversed once at the end)
-        uint32_t w[16];
-#pragma unroll
-        for (int i = 0; i < 16; ++i) w[i] = 0u;
-#define VO_TEST(j, A, B) w[(j) >> 5] = __funnelshift_l(static_cast<uint32_t>(v[B] - v[A]), w[(j) >> 5], 1);
-        VO_FREAK_TEST_LIST(VO_TEST)
-#undef VO_TEST
-#pragma unroll
-        for (int i = 0; i < 16; ++i) w[i] = __brev(w[i]);
-        uint4* __restrict__ out = reinterpret_cast<uint4*>(a.desc + ((size_t)f * a.kp_stride + q) * 16);
-        out[0] = make_uint4(w[0], w[1], w[2], w[3]);
-        out[1] = make_uint4(w[4], w[5], w[6], w[7]);
-        out[2] = make_uint4(w[8], w[9], w[10], w[11]);
-        out[3] = make_uint4(w[12], w[13], w[14], w[15]);
+        if (!SPLIT) describe_keypoint(a, f, q, kp, angle, img, pitch);
     }
 }
 
@@ -257,7 +289,12 @@ cudaError_t freak_upload_tables() {
 cudaError_t launch_freak(const FreakArgs& a, int n_frames, int max_n, cudaStream_t st) {
     if (max_n <= 0) return cudaSuccess;
     const dim3 grid((max_n + FK_KP * FK_NT - 1) / (FK_KP * FK_NT), n_frames);
-    k_freak<<<grid, FK_NT, 0, st>>>(a);
+    if (VO_FK_SPLIT) {
+        k_freak<true><<<grid, FK_NT, 0, st>>>(a);
+        k_describe<<<dim3((max_n + FK_NT - 1) / FK_NT, n_frames), FK_NT, 0, st>>>(a);
+    } else {
+        k_freak<false><<<grid, FK_NT, 0, st>>>(a);
+    }
     return cudaGetLastError();
 }
 
