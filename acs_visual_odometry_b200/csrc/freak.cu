@@ -149,23 +149,18 @@ __global__ void __launch_bounds__(FK_NT, SPLIT ? VO_FK_MINB_ORIENT : VO_FK_MINB)
     {
         const uint8_t* __restrict__ c0 = img + (size_t)(int)kp0.y * a.blur_pitch + (int)kp0.x;
         const uint8_t* __restrict__ c1 = img + (size_t)(int)kp1.y * a.blur_pitch + (int)kp1.x;
-        {
-            const int off = (int)c_py[0] * pitch + (int)c_px[0];
-            s_p[0][t] = (unsigned short)((uint32_t)c0[off] | ((uint32_t)c1[off] << 8));
+        uint32_t b0[VO_FREAK_POINTS], b1[VO_FREAK_POINTS];  // all 86 gathers in flight before the first is used
+#pragma unroll
+        for (int p = 0; p < VO_FREAK_POINTS; ++p) {
+            const int off = (int)c_py[p] * pitch + (int)c_px[p];
+            b0[p] = c0[off]; b1[p] = c1[off];
+            s_p[p][t] = (unsigned short)(b0[p] | (b1[p] << 8));
         }
 #pragma unroll
-        for (int w = 0; w < FK_WINDOWS; ++w) {  // window by window: at most twelve samples live at a time
-            uint32_t lo0 = 0, hi0 = 0, lo1 = 0, hi1 = 0;
-#pragma unroll
-            for (int i = 0; i < FK_GROUP; ++i) {
-                const int p = 1 + FK_GROUP * w + i;
-                const int off = (int)c_py[p] * pitch + (int)c_px[p];
-                const uint32_t x0 = c0[off], x1 = c1[off];
-                s_p[p][t] = (unsigned short)(x0 | (x1 << 8));
-                if (i < 4) { lo0 |= x0 << (8 * i); lo1 |= x1 << (8 * i); }
-                else { hi0 |= x0 << (8 * (i - 4)); hi1 |= x1 << (8 * (i - 4)); }
-            }
-            s_win[w][t] = make_uint4(lo0, hi0, lo1, hi1);
+        for (int w = 0; w < FK_WINDOWS; ++w) {
+            const int r = 1 + FK_GROUP * w;
+            s_win[w][t] = make_uint4(b0[r] | (b0[r + 1] << 8) | (b0[r + 2] << 16) | (b0[r + 3] << 24), b0[r + 4] | (b0[r + 5] << 8),
+                                     b1[r] | (b1[r + 1] << 8) | (b1[r + 2] << 16) | (b1[r + 3] << 24), b1[r + 4] | (b1[r + 5] << 8));
         }
     }
 
