@@ -249,14 +249,32 @@ __global__ void __launch_bounds__(SEL_NT) k_select(const SelectArgs a) {
     }
     __syncthreads();
     for (int k = 128; k <= len; k <<= 1) {
-        for (int j = k >> 1; j >= 64; j >>= 1) {
-            for (int q = tid; q < len; q += SEL_NT) {
-                const int partner = q ^ j;
-                if (partner > q) {
-                    const uint32_t x = s_pos[q], y = s_pos[partner];
-                    const bool up = (q & k) == 0;
-                    if ((x > y) == up) { s_pos[q] = y; s_pos[partner] = x; }
-                }
+        int j = k >> 1;
+        // two distances per barrier: a thread holds the four keys q, q + j/2, q + j, q + 3j/2 and does the two
+        // compare-exchanges of distance j and the two of distance j/2 on them (all four lie in the same run of phase k)
+        for (; j >= 128; j >>= 2) {
+            const int h = j >> 1;
+            for (int qd = tid; qd < (len >> 2); qd += SEL_NT) {
+                const int q = ((qd & ~(h - 1)) << 2) | (qd & (h - 1));
+                uint32_t a0 = s_pos[q], a1 = s_pos[q + h], a2 = s_pos[q + j], a3 = s_pos[q + j + h];
+                const bool up = (q & k) == 0;
+                uint32_t t;
+                if ((a0 > a2) == up) { t = a0; a0 = a2; a2 = t; }
+                if ((a1 > a3) == up) { t = a1; a1 = a3; a3 = t; }
+                if ((a0 > a1) == up) { t = a0; a0 = a1; a1 = t; }
+                if ((a2 > a3) == up) { t = a2; a2 = a3; a3 = t; }
+                s_pos[q] = a0; s_pos[q + h] = a1; s_pos[q + j] = a2; s_pos[q + j + h] = a3;
+            }
+            __syncthreads();
+        }
+        for (; j >= 64; j >>= 1) {
+            // one compare-exchange per thread and trip: pair p of this distance is (q, q + j) with q = p's bits above log2(j)
+            // shifted up by one (every thread works; walking q and skipping the upper partners idled half of them)
+            for (int pr = tid; pr < (len >> 1); pr += SEL_NT) {
+                const int q = ((pr & ~(j - 1)) << 1) | (pr & (j - 1)), partner = q + j;
+                const uint32_t x = s_pos[q], y = s_pos[partner];
+                const bool up = (q & k) == 0;
+                if ((x > y) == up) { s_pos[q] = y; s_pos[partner] = x; }
             }
             __syncthreads();
         }
