@@ -100,6 +100,7 @@ def load_library():
         "vo_match": (i, [vp, i, i, f, i, vp, i, P(i)]),
         "vo_match_host": (i, [vp, vp, i, vp, i, i, f, i, vp, i, P(i)]),
         "vo_match_raw": (i, [vp, vp, i]),
+        "vo_match_static": (i, [vp, i, vp, i, f, i, vp, vp, vp]),  # no context, no allocation: device pointers in and out
         "vo_sequence_run": (i, [vp, vp, i, i, i, sz, sz, P(_CParams), i, P(_CSeqResult)]),
         "vo_sequence_upload": (i, [vp, vp, i, i, i, sz, sz]),
         "vo_sequence_run_resident": (i, [vp, P(_CParams), i]),

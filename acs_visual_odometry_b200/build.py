@@ -14,7 +14,7 @@ PKG = Path(__file__).resolve().parent
 CSRC = PKG / "csrc"
 OBJ = CSRC / "_obj"
 LIB = PKG / "libvofront.so"
-SOURCES = ["api.cu", "stencil.cu", "nms_select.cu", "freak.cu", "match.cu", "stages.cu"]
+SOURCES = ["api.cu", "stencil.cu", "nms_select.cu", "freak.cu", "match.cu", "match_static.cu", "stages.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
          "-Xcompiler", "-fPIC", "-Xptxas", "-v", "--resource-usage"] + os.environ.get("VO_NVCC_EXTRA", "").split()

@@ -227,6 +227,8 @@ int run_seq_chunk(vo_ctx* c, const uint8_t* in_base, size_t in_fstride, size_t i
 
 }  // namespace
 
+void vo_internal_set_thread_error(const std::string& msg) { g_create_err = msg; }
+
 extern "C" {
 
 int vo_params_preset(vo_params* p, int preset) {

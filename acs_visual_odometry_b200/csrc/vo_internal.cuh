@@ -81,6 +81,9 @@ struct vo_ctx {
     std::string err;
 };
 
+// Message behind vo_last_error(NULL) for entry points that work without a context (match_static.cu).
+void vo_internal_set_thread_error(const std::string& msg);
+
 // ---- kernel launchers (each TU owns its kernels) ------------------------------------------------
 struct StencilArgs {
     const uint8_t* in; size_t in_fstride, in_pitch;     // gray (or blurred when from_blurred)

@@ -10,7 +10,7 @@
  * Conventions
  *   - every function returning int returns VO_OK (0) or a negative VO_ERR_* code;
  *     vo_last_error(ctx) gives a human-readable message for the last failure on that context
- *     (ctx == NULL: last vo_create() failure on this thread).  Nothing throws across the ABI.
+ *     (ctx == NULL: last vo_create() or vo_match_static() failure on this thread).  Nothing throws across the ABI.
  *   - a vo_ctx belongs to one GPU; it is not thread-safe, independent contexts are fully concurrent.
  *   - images are 8-bit grayscale, row-major, `pitch` bytes between rows (pitch >= cols).
  *   - keypoints are (x = column, y = row) float pairs, sorted by (y, x) ascending, exactly the order
@@ -165,6 +165,38 @@ int vo_match_host(vo_ctx* ctx, const uint8_t* d1, int n1, const uint8_t* d2, int
 /* Per-query (best distance, best index, second-best distance) triples of the last vo_match /
  * vo_match_host call: n1 x 3 int32; INT32_MAX / -1 where undefined (fewer than 1 / 2 train rows). */
 int vo_match_raw(vo_ctx* ctx, int32_t* raw, int n1);
+
+/* ---- matching without any allocation -----------------------------------------------------------
+ * No counterpart in the reference: this entry point exists only because of how this library manages GPU memory.
+ * Everything above needs a vo_ctx, and vo_create() obtains the context's pools - the matcher's scratch among them -
+ * with cudaMalloc.  vo_match_static is for callers that cannot do that: processes whose device memory is handed out
+ * entirely by an arena of their own (fixed per-module budgets on a robot, an inference server's allocator), loops with
+ * a latency bound (cudaMalloc / cudaFree synchronise the device and take an unpredictable time), and plug-ins that get
+ * device pointers and a stream from a host application and may not create device state of their own.  It needs no
+ * context and calls no cudaMalloc, cudaFree or other allocating routine, on any call.
+ *
+ * Same result as vo_match_host on the same descriptors (same keys, same merge, same fp32 ratio test): the accepted
+ * (queryIdx, trainIdx) pairs ascending in queryIdx.  The caller passes inputs and outputs, all DEVICE memory of the
+ * current GPU (host pointers are refused with VO_ERR_BAD_ARG):
+ *   d_query, d_train   packed descriptors, n x 16 uint32 (may be NULL when the count is 0)
+ *   d_pairs            room for n1 pairs (2 * n1 int32): a query yields at most one match
+ *   d_n_out            one int32, the number of pairs written
+ *   stream             a cudaStream_t (NULL = the default stream).  The call only enqueues two kernels; synchronise the
+ *                      stream before reading the outputs.
+ * The scratch between the two kernels (8 x n1 key pairs) lives in an array compiled into the library, 512 KB, sized for
+ * VO_STATIC_MATCH_MAX descriptors per side; larger counts are refused with VO_ERR_BAD_ARG (use a context for those).
+ * Every GPU that loads the library holds that array until the process exits.
+ *   - The first call on each GPU looks up the array's device address (cudaGetSymbolAddress, which also makes the
+ *     runtime load the library's device code on that GPU).  Make that first call during start-up, before any stream
+ *     capture and outside the latency-critical part; later calls on that GPU only launch.
+ *   - All calls on one GPU share the array, and it keeps the contents of the last call.  Nothing in it has to start at
+ *     zero (every entry the second kernel reads is written by the first kernel of the same call), but two calls that
+ *     overlap on the GPU - different streams, or different host threads on different streams - race on it and give
+ *     wrong matches.  Keep all calls on one stream, or order them with events.
+ * Errors: vo_last_error(NULL) on the calling thread. */
+#define VO_STATIC_MATCH_MAX 8192
+int vo_match_static(const uint32_t* d_query, int n1, const uint32_t* d_train, int n2, float ratio, int match_bits,
+                    int32_t* d_pairs, int32_t* d_n_out, void* stream);
 
 /* ---- frame sequences (the batched, pipelined form of VisualOdometry::run's front-end half) -------
  * VisualOdometry.cpp:64-100: extract every frame, match frame i-1 (query) against frame i (train).
