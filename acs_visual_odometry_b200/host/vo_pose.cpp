@@ -305,7 +305,12 @@ PoseResult PoseUpdate::getPoseEx(const Mat3& F, const std::vector<Point2f>& poin
     // the largest count.  Two things make that cheaper without changing the winner or its count:
     //  * (R, -t) needs no triangulation of its own.  Its DLT matrix is the one of (R, t) with the last column negated
     //    (the rows of view 1 have a zero there), so its null vector is (x, y, z, -w): the homogenised point, z1 and z2
-    //    all change sign exactly, and its vote is "both depths negative" on the triangulation of (R, t);
+    //    all change sign, and its vote is "both depths negative" on the triangulation of (R, t).  That equals a separate
+    //    triangulation of [R|-t] - what the reference does - up to the solver's tolerance, not bit for bit: the inverse
+    //    iteration starts from a fixed vector, not the mirrored one, so the two null vectors agree to about 1e-11 before
+    //    the float cast and a point with |w| at 1e-6 or a depth at 0 can vote differently.  On near-degenerate data
+    //    (millimetre baselines, a third of the points near infinity) winner and count still equal four brute-force
+    //    triangulations (tests/test_host.py::test_cheirality_shortcut_against_four_triangulations);
     //  * only the argmax and its count are used afterwards, so a rotation is dropped as soon as neither of its candidates
     //    can reach the leader's count even if every remaining point voted for it (its partial counts are then below the
     //    winner's and cannot be chosen).

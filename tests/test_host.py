@@ -45,6 +45,12 @@ def test_host_library_exports_every_declared_symbol():
     host.load_host_library()
 
 
+def test_pipeline_release_with_nothing_kept_is_a_no_op():
+    """vo_pipeline_release before any run: no context, an empty pool, nothing to hand back - and no CUDA call."""
+    host.pipeline_release()
+    host.pipeline_release()
+
+
 def test_fundamental_matches_restatement():
     for seed, n in ((1, 8), (2, 8), (3, 40), (4, 300)):
         pts = scene(n, rot([0.1, 1, 0.05], 0.03), np.array([0.1, -0.02, 1.0]), seed, noise=0.3)
@@ -111,6 +117,40 @@ def test_get_pose_matches_restatement_and_truth():
     with pytest.raises(host.VoHostError) as e:
         host.get_pose(np.array([[0, -1.0, 0], [1.0, 0, 0], [0, 0, 0]]), pts[:, :2], pts[:, 2:], K=np.eye(3))
     assert "Degenerate" in str(e.value)
+
+
+def test_cheirality_shortcut_against_four_triangulations():
+    """getPose takes the votes of (R, -t) from the triangulation of (R, t) and stops triangulating a rotation that cannot
+    win (vo_pose.cpp); the reference triangulates all four candidates (PoseUpdate.hpp:98-146).  The two agree up to the
+    solver's tolerance, so the place to look for a difference is data where votes hang on |w| ~ 1e-6 or depth ~ 0:
+    baselines down to a millimetre, a third of the points between 2 km and 1000 km away, half-pixel noise.  Winner and
+    count are compared with oracle/host_oracle.py's four brute-force triangulations: the count within 2 votes (borderline
+    points may fall either way), the selected (R, t) exactly whenever the brute-force margin is larger than that slack."""
+    checked = 0
+    for seed in range(8):
+        for base in (1.0, 0.02, 0.001):
+            for ang in (0.01, 0.0003):
+                rng = np.random.default_rng(100 + seed)
+                n = 600
+                R = rot([0.1, 1, 0.05], ang)
+                t = np.array([0.2, -0.05, 1.0]); t = t / np.linalg.norm(t) * base
+                X = np.c_[rng.uniform(-8, 8, n), rng.uniform(-2, 2, n), rng.uniform(6, 40, n)]
+                X[:n // 3, 2] = rng.uniform(2000, 1e6, n // 3)
+                X[:n // 3, :2] *= X[:n // 3, 2:3] / 20
+                x1, x2 = X @ K.T, (X @ R.T + t) @ K.T
+                p1 = (x1[:, :2] / x1[:, 2:] + rng.normal(0, 0.5, (n, 2))).astype(np.float32)
+                p2 = (x2[:, :2] / x2[:, 2:] + rng.normal(0, 0.5, (n, 2))).astype(np.float32)
+                tu = t / np.linalg.norm(t)
+                tx = np.array([[0, -tu[2], tu[1]], [tu[2], 0, -tu[0]], [-tu[1], tu[0], 0]])
+                F = np.linalg.inv(K).T @ tx @ R @ np.linalg.inv(K)
+                Rg, tg, votes = host.get_pose(F, p1, p2, gt_step=1.0)
+                Ro, to, votes_o = ho.get_pose(F, p1, p2, 1.0)
+                top = sorted(votes_o)
+                assert abs(votes - top[-1]) <= 2, (seed, base, ang, votes, votes_o)
+                if top[-1] - top[-2] > 4:
+                    assert np.allclose(Rg, Ro, atol=1e-9) and np.allclose(tg, to, atol=1e-9), (seed, base, ang, votes, votes_o)
+                    checked += 1
+    assert checked >= 24
 
 
 def test_get_pose_against_opencv_golden():
