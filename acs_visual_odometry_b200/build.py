@@ -54,6 +54,18 @@ def build(force=False, verbose=False):
     return LIB
 
 
+def source_hash(name="stencil.cu"):
+    """SHA-1 of a kernel source with comments and white space removed: changes when the code changes, not when a comment
+    does.  profiles/stencil_traffic.json records it for the source its ncu counters were captured from; bench.py refuses
+    to quote those counters for any other code (`traffic: null, traffic_stale: true`)."""
+    import hashlib
+    import re
+    text = (CSRC / name).read_text()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    text = re.sub(r"//[^\n]*", "", text)
+    return hashlib.sha1(re.sub(r"\s+", "", text).encode()).hexdigest()
+
+
 HOST = PKG / "host"
 HOST_LIB = PKG / "libvohost.so"
 HOST_MAIN = PKG / "vo_main"

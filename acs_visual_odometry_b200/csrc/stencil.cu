@@ -255,8 +255,13 @@ k_stencil(const StencilArgs a, int n_strips, int n_segs, int seg_rows, int n_tas
     const int f = gtask / per_frame, task = gtask - f * per_frame;
     const int strip = task % n_strips, seg = task / n_strips;
     const int H = a.rows, W = a.cols;
-    // rows this task owns (blurred rows it stores, NMS centres it decides) and rows it computes: a fused segment also
-    // computes the four response rows either side of its own (its windows reach NMSH <= 2 rows across the border)
+    // rows this task owns (the NMS centres it decides) and rows it computes: a fused segment also computes the four
+    // response rows either side of its own (its windows reach NMSH <= 2 rows across the border).  Blurred rows are stored
+    // for every COMPUTED row (the store guard below is [ys, ye), and every steady trip), so the two tasks either side of
+    // a seam both write its 8 halo rows - the same bytes, a benign write-write overlap that costs 8 / seg_rows extra
+    // store requests.  The 2 B/px quoted for the fused form holds where it is quoted: 1000 KITTI frames per launch
+    // plan ONE segment per strip (launch_stencil: best_segs = 1), so there is no seam; small batches (several segments
+    // of >= 48 rows) pay up to 1/6 more blurred stores.
     const int ys_own = seg * seg_rows, ye_own = min(H, ys_own + seg_rows);
     const int ys = FUSED ? max(0, ys_own - RB) : ys_own, ye = FUSED ? min(H, ye_own + RB) : ye_own;
     const int xs = FUSED ? strip * SWF - HXF : strip * SW - HX;

@@ -248,6 +248,14 @@ def stencil_capture():
     return json.loads(tp.read_text()) if tp.exists() else {}
 
 
+def capture_applies(cap, nb, rows, cols, code_sha1):
+    """(use, stale): the committed counters are quoted only for the launch shape AND the stencil code they were captured
+    from (`stencil_code_sha1`, a comment-insensitive hash of stencil.cu); same shape but other code = stale."""
+    shape = (cap.get("batch"), cap.get("rows"), cap.get("cols")) == (nb, rows, cols)
+    code = cap.get("stencil_code_sha1") == code_sha1
+    return shape and code, shape and not code
+
+
 def stencil_rooflines(vo, params, cfg, nb, fused_ms_in_step, peak, peak_src, sm_mhz):
     """The two labelled rooflines of the stencil kernel over `nb` frames per launch."""
     px = cfg["rows"] * cfg["cols"] * nb
@@ -257,8 +265,9 @@ def stencil_rooflines(vo, params, cfg, nb, fused_ms_in_step, peak, peak_src, sm_
         cands = vo.bench_candidates(nb)
     except Exception:  # windows 7 / 9 and tiny images have no fused form
         fused_alone_ms, cands = None, 0
+    from acs_visual_odometry_b200.build import source_hash
     cap = stencil_capture()
-    same = (cap.get("batch"), cap.get("rows"), cap.get("cols")) == (nb, cfg["rows"], cfg["cols"])
+    same, stale = capture_applies(cap, nb, cfg["rows"], cfg["cols"], source_hash("stencil.cu"))
     issue_peak = 148 * 4 * 32 * (sm_mhz or 1965.0) * 1e6  # lane-instructions/s: 4 schedulers per SM, one warp instruction per clock each
 
     def block(kind, label, bpp, extra, ms, timed):
@@ -270,6 +279,8 @@ def stencil_rooflines(vo, params, cfg, nb, fused_ms_in_step, peak, peak_src, sm_
              "algorithmic_bytes_per_launch": alg, "bytes_per_px": bpp, "avg_launch_ms": ms, "timed": timed, "peak_source": peak_src,
              "traffic": None}
         c = cap.get(kind) if same else None
+        if stale:
+            b["traffic_stale"] = True  # the committed ncu counters belong to other stencil code: not quoted
         if c:
             b["traffic"] = c["dram_bytes_per_launch"]
             b["traffic_source"] = cap.get("source")

@@ -39,3 +39,31 @@ def test_reference_arm_is_silent_on_other_ranks():
     out = subprocess.run([sys.executable, str(ROOT / "bench.py"), "--impl", "reference", "--gpus", "2"], capture_output=True, text=True,
                          timeout=120, env=env)
     assert out.returncode == 0 and out.stdout.strip() == ""
+
+
+def test_committed_stencil_counters_are_tied_to_the_code_they_were_captured_from(tmp_path, monkeypatch):
+    """roofline.traffic and the issue block come from a committed ncu capture (profiles/stencil_traffic.json).  bench.py
+    quotes them only for the launch shape and the stencil code of the capture: the file records a hash of stencil.cu
+    that ignores comments and white space, and other code gives `traffic: null` + `traffic_stale: true`."""
+    import importlib.util
+    from acs_visual_odometry_b200 import build
+    spec = importlib.util.spec_from_file_location("bench_mod", ROOT / "bench.py")
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    cap = json.loads((ROOT / "profiles" / "stencil_traffic.json").read_text())
+    h = cap["stencil_code_sha1"]
+    assert len(h) == 40
+    shape = (cap["batch"], cap["rows"], cap["cols"])
+    assert bench.capture_applies(cap, *shape, h) == (True, False)
+    assert bench.capture_applies(cap, *shape, "0" * 40) == (False, True)            # same shape, other code: stale
+    assert bench.capture_applies(cap, 64, cap["rows"], cap["cols"], h) == (False, False)   # other shape: simply no capture
+    assert bench.capture_applies({}, *shape, h) == (False, False)
+    # the hash sees code, not comments or layout
+    src = (build.CSRC / "stencil.cu").read_text()
+    monkeypatch.setattr(build, "CSRC", tmp_path)
+    (tmp_path / "stencil.cu").write_text(src)
+    base = build.source_hash("stencil.cu")
+    (tmp_path / "stencil.cu").write_text("// a new comment\n" + src.replace("\n", "\n  \n") + "/* trailing\n block */\n")
+    assert build.source_hash("stencil.cu") == base
+    (tmp_path / "stencil.cu").write_text(src.replace("constexpr int RB = 4", "constexpr int RB = 8", 1) + "\nint extra_symbol;\n")
+    assert build.source_hash("stencil.cu") != base

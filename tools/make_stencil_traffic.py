@@ -14,7 +14,12 @@ rows = list(csv.reader(open(sys.argv[1])))
 hdr, body = rows[0], rows[2:]
 ix = {h: i for i, h in enumerate(hdr)}
 units = rows[1]
-out = {"batch": int(sys.argv[2]), "rows": int(sys.argv[3]), "cols": int(sys.argv[4]), "source": sys.argv[5]}
+sys.path.insert(0, str(__import__("pathlib").Path(__file__).resolve().parents[1]))
+from acs_visual_odometry_b200.build import source_hash  # noqa: E402
+
+# the hash is taken from the working tree: run this tool on the code the capture ran
+out = {"batch": int(sys.argv[2]), "rows": int(sys.argv[3]), "cols": int(sys.argv[4]), "source": sys.argv[5],
+       "stencil_code_sha1": source_hash("stencil.cu")}
 
 
 def scale(col):
