@@ -11,7 +11,7 @@ _PKG = Path(__file__).resolve().parent
 
 SYMBOLS = ["vo_host_fundamental", "vo_host_normalize_points", "vo_host_score", "vo_host_triangulate", "vo_host_sampson", "vo_host_ransac", "vo_host_get_pose", "vo_host_read_gt_line",
            "vo_host_format_pose_csv", "vo_host_euler", "vo_host_read_gray", "vo_host_write_png", "vo_host_write_pgm",
-           "vo_pipeline_run", "vo_pipeline_run_ex", "vo_host_last_error"]
+           "vo_pipeline_run", "vo_pipeline_run_ex", "vo_pipeline_release", "vo_host_last_error"]
 
 
 class VoHostError(RuntimeError):
@@ -168,3 +168,8 @@ def pipeline_run(image_dir, num_images, pose_file, output_csv, num_threads=8, de
                                                str(output_csv).encode(), preset, batch, C.c_uint64(seed), int(bool(reuse_model)),
                                                _dp(stats)))
     return dict(zip(STAT_KEYS, stats.tolist()))
+
+
+def pipeline_release():
+    """vo_pipeline_release: drop the GPU context and the pooled page-locked buffers pipeline_run keeps between calls."""
+    _ck(load_host_library().vo_pipeline_release())

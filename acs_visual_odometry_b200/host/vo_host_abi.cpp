@@ -226,4 +226,16 @@ int vo_pipeline_run_ex(int device, int num_threads, const char* image_dir, int n
     });
 }
 
+int vo_pipeline_release(void) {
+    return guarded([&] {
+        {
+            std::lock_guard<std::mutex> lk(g_ctx_mutex);
+            if (g_ctx.ctx) vo_destroy(g_ctx.ctx);
+            g_ctx = vo::VisualOdometry::Context();
+        }
+        vo::release_pinned_pool();
+        return 0;
+    });
+}
+
 }  // extern "C"

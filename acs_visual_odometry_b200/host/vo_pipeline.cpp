@@ -1,9 +1,11 @@
 // vo_pipeline.cpp — see vo_pipeline.hpp.  Calls the GPU front end only through the C ABI (include/vofront.h).
 #include "vo_pipeline.hpp"
 
+#include <algorithm>
 #include <atomic>
 #include <chrono>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <future>
 #include <mutex>
@@ -33,19 +35,30 @@ void parallel_for(size_t n, size_t threads, Fn fn) {
 
 // Page-locked staging buffers are expensive to create (the driver pins every page) and a run needs about 100 MB of
 // them: they are kept in a process-wide pool between runs, like the GPU context (a second sequence through
-// vo_pipeline_run pays neither again).  Never returned to the driver before the process ends.
+// vo_pipeline_run pays neither again).  The pool is bounded: a block serves a request only when it is at most twice
+// the size asked for (a frame-sized block is never spent on a 260-byte count array), blocks coming back beyond
+// VO_PINNED_POOL_MB (default 1024) of pooled memory go back to the driver, oldest first, and release_pinned_pool()
+// (vo_pipeline_release in the C ABI) returns everything.
 struct PinnedPool {
     std::mutex m;
-    std::vector<std::pair<void*, size_t>> free_blocks;
+    std::vector<std::pair<void*, size_t>> free_blocks;  // oldest first
+    size_t pooled = 0, cap = 0;
+    PinnedPool() {
+        const char* e = std::getenv("VO_PINNED_POOL_MB");
+        cap = static_cast<size_t>(e ? std::max(0L, std::atol(e)) : 1024L) << 20;
+    }
     void* acquire(size_t bytes, size_t* got) {
         {
             std::lock_guard<std::mutex> lk(m);
-            size_t best = free_blocks.size();  // best fit: the smallest block that is large enough
-            for (size_t i = 0; i < free_blocks.size(); ++i)
-                if (free_blocks[i].second >= bytes && (best == free_blocks.size() || free_blocks[i].second < free_blocks[best].second)) best = i;
+            size_t best = free_blocks.size();  // best fit: the smallest block that is large enough, and not wastefully so
+            for (size_t i = 0; i < free_blocks.size(); ++i) {
+                const size_t sz = free_blocks[i].second;
+                if (sz >= bytes && sz / 2 <= bytes && (best == free_blocks.size() || sz < free_blocks[best].second)) best = i;
+            }
             if (best < free_blocks.size()) {
                 void* p = free_blocks[best].first;
                 *got = free_blocks[best].second;
+                pooled -= *got;
                 free_blocks.erase(free_blocks.begin() + best);
                 return p;
             }
@@ -55,8 +68,29 @@ struct PinnedPool {
     }
     void release(void* p, size_t bytes) {
         if (!p) return;
-        std::lock_guard<std::mutex> lk(m);
-        free_blocks.emplace_back(p, bytes);
+        std::vector<void*> drop;
+        {
+            std::lock_guard<std::mutex> lk(m);
+            free_blocks.emplace_back(p, bytes);
+            pooled += bytes;
+            while (pooled > cap && !free_blocks.empty()) {
+                drop.push_back(free_blocks.front().first);
+                pooled -= free_blocks.front().second;
+                free_blocks.erase(free_blocks.begin());
+            }
+        }
+        for (void* q : drop) vo_host_free(q);
+    }
+    size_t trim() {
+        std::vector<std::pair<void*, size_t>> all;
+        {
+            std::lock_guard<std::mutex> lk(m);
+            all.swap(free_blocks);
+            pooled = 0;
+        }
+        size_t bytes = 0;
+        for (auto& b : all) { vo_host_free(b.first); bytes += b.second; }
+        return bytes;
     }
 };
 PinnedPool& pinned_pool() {
@@ -70,6 +104,8 @@ void check(vo_ctx* ctx, int rc, const char* what) {
 }
 
 }  // namespace
+
+size_t release_pinned_pool() { return pinned_pool().trim(); }
 
 struct VisualOdometry::PairResult {
     enum Status { OK, FEW_MATCHES, FEW_INLIERS, DEGENERATE } status = FEW_MATCHES;
@@ -313,7 +349,7 @@ void VisualOdometry::run(const std::string image_dir, const size_t num_images, c
             check(ctx_, vo_sequence_flags(ctx_, flags.data(), n), "vo_sequence_flags");
             for (int k = 0; k < n; ++k) {
                 if (!(flags[k] & 1)) continue;
-                ++stats.capacity_frames;
+                if (k > 0 || c.first == 1) ++stats.capacity_frames;  // ids[0] of a later chunk was counted as the last frame of the one before
                 c.nkp[k] = 0;
                 if (k > 0) c.nmatch[k - 1] = 0;
                 if (k + 1 < n) c.nmatch[k] = 0;
@@ -368,12 +404,21 @@ void VisualOdometry::run(const std::string image_dir, const size_t num_images, c
                 ++stats.respeculated;
                 const int sa = 2 * (batch + 1), sb = sa + 1;
                 int na = 0, nb = 0, nm = 0;
-                check(ctx_, vo_extract(ctx_, anchor.data(), rows, cols, static_cast<size_t>(cols), &params, sa), "vo_extract");
-                check(ctx_, vo_extract(ctx_, c.pixels + j * fbytes, rows, cols, static_cast<size_t>(cols), &params, sb), "vo_extract");
-                check(ctx_, vo_frame_fetch(ctx_, sa, &na, kpa.data(), nullptr, nullptr), "vo_frame_fetch");
-                check(ctx_, vo_frame_fetch(ctx_, sb, &nb, kpb.data(), nullptr, nullptr), "vo_frame_fetch");
-                check(ctx_, vo_match(ctx_, sa, sb, params.ratio, params.match_bits, prs.data(), maxkp, &nm), "vo_match");
-                solve_pair(kpa.data(), kpb.data(), prs.data(), nm, i, r);
+                // A frame that overflows its candidate list does so here as well as on the chunk path (same pixels, same
+                // parameters), where it was flagged and counted: VO_ERR_CAPACITY from any of these calls makes the pair one
+                // without matches (r stays FEW_MATCHES, VisualOdometry.cpp:108-115), every other error still ends the run.
+                bool overflow = false;
+                auto soft = [&](int rc, const char* what) {
+                    if (rc == VO_ERR_CAPACITY) overflow = true;
+                    else check(ctx_, rc, what);
+                    return !overflow;
+                };
+                if (soft(vo_extract(ctx_, anchor.data(), rows, cols, static_cast<size_t>(cols), &params, sa), "vo_extract") &&
+                    soft(vo_extract(ctx_, c.pixels + j * fbytes, rows, cols, static_cast<size_t>(cols), &params, sb), "vo_extract") &&
+                    soft(vo_frame_fetch(ctx_, sa, &na, kpa.data(), nullptr, nullptr), "vo_frame_fetch") &&
+                    soft(vo_frame_fetch(ctx_, sb, &nb, kpb.data(), nullptr, nullptr), "vo_frame_fetch") &&
+                    soft(vo_match(ctx_, sa, sb, params.ratio, params.match_bits, prs.data(), maxkp, &nm), "vo_match"))
+                    solve_pair(kpa.data(), kpb.data(), prs.data(), nm, i, r);
             }
             stats.ransac_iterations += r.iterations;
             sum_m += r.n_matches; ++n_m;

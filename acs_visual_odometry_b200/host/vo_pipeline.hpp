@@ -91,4 +91,7 @@ private:
     std::vector<Mat4> estimated_poses_;
 };
 
+// Returns the pooled page-locked staging buffers of finished runs to the driver; the number of bytes freed.
+size_t release_pinned_pool();
+
 }  // namespace vo

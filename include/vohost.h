@@ -67,6 +67,11 @@ int vo_pipeline_run(int device, int num_threads, const char* image_dir, int num_
 #define VO_PIPE_REUSE_MODEL 1
 int vo_pipeline_run_ex(int device, int num_threads, const char* image_dir, int num_images, const char* pose_file,
                        const char* output_csv, int preset, int batch, uint64_t seed, int flags, double* stats);
+/* Gives back what vo_pipeline_run keeps between calls: the GPU context of the last run (all its device memory) and the
+ * pooled page-locked staging buffers.  For long-lived processes that are done with the pipeline for a while; the next
+ * vo_pipeline_run simply builds both again.  The pool is bounded in any case: at most VO_PINNED_POOL_MB (environment,
+ * default 1024) megabytes stay pooled, and a pooled block is reused only for requests of at least half its size. */
+int vo_pipeline_release(void);
 /* message of the last failure on this thread */
 const char* vo_host_last_error(void);
 

@@ -168,3 +168,50 @@ def test_candidate_overflow_is_a_failed_frame_not_a_failed_run(tmp_path, scene24
     want, log = run_loop(blank, gt[:8], *oracle_stages(oracle, 8, SEED))
     assert [e["status"] for e in log[1:]] == ["ok", "ok", "ok", "few_matches", "ok", "ok", "ok"]
     np.testing.assert_allclose(read_csv_poses(tmp_path / "est.csv"), want, rtol=2e-8, atol=1e-9)
+
+
+def test_consecutive_overflowing_frames_across_a_chunk_boundary(tmp_path, scene24, oracle):
+    """Two overflowing frames in a row, the second one the last frame of chunk 0 and therefore also the carried-over
+    first frame of chunk 1 (batch 5: chunk 0 = frames 1..5, chunk 1 = frames 6..7 behind frame 5).  The pair after the
+    first failure goes through the on-demand re-match (last valid frame, frame 5), which extracts the overflowing frame
+    again: that must be a failed pair, not the end of the run, and the counter must count distinct frames."""
+    from acs_visual_odometry_b200 import Params
+    frames, gt = scene24
+    fr = [f.copy() for f in frames[:8]]
+    rng = np.random.default_rng(3)
+    for k in (4, 5):
+        fr[k] = rng.integers(0, 256, fr[k].shape, dtype=np.uint8)
+    p = Params.vo_gpu_ref()
+    cands = [len(oracle.nms(oracle.response(oracle.blur(f), 20000.0), 3, 1 << 20)) for f in fr]
+    scene_max = max(c for i, c in enumerate(cands) if i not in (4, 5))
+    cap = int(0.5 * (scene_max + min(cands[4], cands[5])))
+    assert min(cands[4], cands[5]) > 2 * scene_max and cap >= p.max_keypoints, cands
+    image_dir, pose_file = write_sequence(tmp_path, fr, gt[:8])
+    import os
+    os.environ["VO_CAND_CAP"] = str(cap)
+    try:
+        st = host.pipeline_run(image_dir, 8, pose_file, tmp_path / "est.csv", num_threads=8, batch=5, seed=SEED)
+    finally:
+        del os.environ["VO_CAND_CAP"]
+    assert st["capacity_frames"] == 2 and st["skipped_frames"] == 2 and st["pairs_ok"] == 5, st
+    assert st["rematched_pairs"] == 2          # (3, 5) over the overflowing frame, then (3, 6)
+    blank = [f if i not in (4, 5) else np.full_like(f, 128) for i, f in enumerate(fr)]
+    want, log = run_loop(blank, gt[:8], *oracle_stages(oracle, 8, SEED))
+    assert [e["status"] for e in log[1:]] == ["ok", "ok", "ok", "few_matches", "few_matches", "ok", "ok"]
+    np.testing.assert_allclose(read_csv_poses(tmp_path / "est.csv"), want, rtol=2e-8, atol=1e-9)
+
+
+def test_pipeline_release_then_run_again(tmp_path, scene24):
+    """vo_pipeline_release hands the kept GPU context and the pooled pinned buffers back; the next run rebuilds both and
+    gives the same trajectory.  Also with the pool capped at zero (VO_PINNED_POOL_MB is read when the pool is first
+    used, so here it only checks that release-and-reacquire cycles keep working)."""
+    image_dir, pose_file = write_sequence(tmp_path, list(scene24[0][:8]), scene24[1][:8])
+    st1 = host.pipeline_run(image_dir, 8, pose_file, tmp_path / "a.csv", num_threads=4, batch=5, seed=SEED)
+    host.pipeline_release()
+    st2 = host.pipeline_run(image_dir, 8, pose_file, tmp_path / "b.csv", num_threads=4, batch=3, seed=SEED)   # other chunk geometry
+    host.pipeline_release()
+    host.pipeline_release()
+    st3 = host.pipeline_run(image_dir, 8, pose_file, tmp_path / "c.csv", num_threads=4, batch=5, seed=SEED)
+    assert st1["pairs_ok"] == st2["pairs_ok"] == st3["pairs_ok"] == 7
+    a, b, c = (read_csv_poses(tmp_path / f"{n}.csv") for n in "abc")
+    assert np.array_equal(a, c) and np.array_equal(a, b)
