@@ -19,9 +19,11 @@
 // for every non-zero C-ABI status.  Empty descriptor sets give an empty match list (feature_matching_parallel.cpp:57).
 // `thread_pool&` and `numThreads` are accepted and ignored: CUDA streams replace the pool.
 #pragma once
+#include <algorithm>
 #include <cstdint>
 #include <cstring>
 #include <memory>
+#include <mutex>
 #include <stdexcept>
 #include <string>
 #include <utility>
@@ -76,13 +78,34 @@ struct Context {
     }
 };
 
-// Process-wide context for the thread_pool overloads (which carry no GPU handle); grown on demand.
-inline Context& default_context(int rows, int cols, int max_kp) {
+// Process-wide context for the thread_pool overloads (which carry no GPU handle); grown on demand.  Callers get a COPY
+// (the handles are shared_ptrs): growing the context for another thread's larger image replaces the process-wide one
+// but cannot destroy the context a thread is still working with - that one dies with its last copy.  The reference's
+// managers are not re-entrant either (they share a thread_pool), and neither is a vo_ctx: two threads that call in with
+// the SAME geometry share one context and must serialise their calls; this only makes differing geometries safe.
+inline Context default_context(int rows, int cols, int max_kp) {
+    static std::mutex m;
     static Context c;
+    std::lock_guard<std::mutex> lk(m);
     if (!c.fits(rows, cols, max_kp))
         c = Context(0, rows > c.max_rows ? rows : (c.max_rows > 64 ? c.max_rows : 64), cols > c.max_cols ? cols : (c.max_cols > 64 ? c.max_cols : 64),
                     max_kp > c.max_keypoints ? max_kp : (c.max_keypoints > 2000 ? c.max_keypoints : 2000));
     return c;
+}
+
+// What the context-less entry points (thread_pool signatures, static stage workers) hold for the length of one call: the
+// process-wide context AND a process-wide lock, because a vo_ctx serves one call at a time.  Calls from several threads
+// therefore queue up instead of racing - on one GPU context they could not overlap anyway.  Re-entrant on a thread.
+struct DefaultCall {
+    std::unique_lock<std::recursive_mutex> lock;
+    Context c;
+    operator const Context&() const { return c; }
+    vo_ctx* get() const { return c.get(); }
+};
+inline DefaultCall default_call(int rows, int cols, int max_kp) {
+    static std::recursive_mutex m;
+    std::unique_lock<std::recursive_mutex> lk(m);
+    return DefaultCall{std::move(lk), default_context(rows, cols, max_kp)};
 }
 
 using Descriptors = std::vector<std::vector<uint8_t>>;  // n x 512 bytes, one 0/1 byte per test (the reference layout)
@@ -106,17 +129,17 @@ inline bool pack_rows(const Descriptors& d, std::vector<uint32_t>& packed) {
     return (bad & 0xFEFEFEFEFEFEFEFEull) == 0;  // false: some byte is neither 0 nor 1
 }
 inline const uint64_t* expand_table() {
-    static uint64_t lut[256];
-    static bool ready = false;
-    if (!ready) {
-        for (int b = 0; b < 256; ++b) {
-            uint64_t v = 0;
-            for (int i = 0; i < 8; ++i) v |= (uint64_t)((b >> i) & 1) << (8 * i);
-            lut[b] = v;
+    struct Lut {
+        uint64_t v[256];
+        Lut() {
+            for (int b = 0; b < 256; ++b) {
+                v[b] = 0;
+                for (int i = 0; i < 8; ++i) v[b] |= (uint64_t)((b >> i) & 1) << (8 * i);
+            }
         }
-        ready = true;
-    }
-    return lut;
+    };
+    static const Lut lut;  // function-local static: initialised once, thread-safe since C++11
+    return lut.v;
 }
 
 // One synchronous fetch of keypoints and PACKED descriptors (64 bytes each instead of 512 over PCIe); the reference's
@@ -240,7 +263,7 @@ inline std::pair<std::vector<std::vector<uint8_t>>, std::vector<cv::KeyPoint>> f
 
 inline std::pair<std::vector<std::vector<uint8_t>>, std::vector<cv::KeyPoint>> feature_extraction_manager_with_points(
     cv::Mat& image, thread_pool& /*pool: replaced by CUDA streams*/) {
-    return vofront::extract(vofront::default_context(image.rows, image.cols, 2000), image, VO_PRESET_CPU_REF);
+    return vofront::extract(vofront::default_call(image.rows, image.cols, 2000), image, VO_PRESET_CPU_REF);
 }
 
 inline std::vector<std::pair<int, int>> matchCustomBinaryDescriptorsThreadPool(
@@ -249,7 +272,7 @@ inline std::vector<std::pair<int, int>> matchCustomBinaryDescriptorsThreadPool(
     if (desc1.empty() || desc2.empty()) return {};
     const int n = (int)(desc1.size() > desc2.size() ? desc1.size() : desc2.size());
     // the SAME process-wide context the thread_pool extraction overload uses (grown only if a set is larger than it holds)
-    return vofront::match(vofront::default_context(1, 1, n), desc1, desc2, ratioThreshold);
+    return vofront::match(vofront::default_call(1, 1, n), desc1, desc2, ratioThreshold);
 }
 // Same, on an explicit context (what a VisualOdometry built around GPU_settings calls).
 inline std::vector<std::pair<int, int>> matchCustomBinaryDescriptorsThreadPool(
@@ -281,7 +304,7 @@ public:
     // corner_detection_parallel.cpp:14-28
     static cv::Mat custom_bgr2gray(cv::Mat& picture) {
         if (picture.channels() != 3) throw std::runtime_error("custom_bgr2gray: 8-bit BGR expected");
-        vofront::Context& c = vofront::default_context(picture.rows, picture.cols, 2000);
+        const vofront::DefaultCall c = vofront::default_call(picture.rows, picture.cols, 2000);
         cv::Mat out(picture.rows, picture.cols, CV_8UC1);
         vofront::check(vo_bgr2gray(c.get(), picture.data, picture.rows, picture.cols, picture.step, out.data), c.get(), "vo_bgr2gray");
         return out;
@@ -289,7 +312,7 @@ public:
     // :30-58.  Jx, Jy, Jxy: CV_32F matrices of the picture's size (the manager allocates them with cv::Mat::zeros,
     // feature_extraction_parallel.cpp:229-231); only rows/columns strictly inside the interval are written.
     static void direction_gradients_worker(const cv::Mat& picture, const interval& iv, cv::Mat& Jx, cv::Mat& Jy, cv::Mat& Jxy) {
-        vofront::Context& c = vofront::default_context(picture.rows, picture.cols, 2000);
+        const vofront::DefaultCall c = vofront::default_call(picture.rows, picture.cols, 2000);
         for (const cv::Mat* m : {&Jx, &Jy, &Jxy})
             if (m->rows != picture.rows || m->cols != picture.cols || m->step != (size_t)picture.cols * 4)
                 throw std::runtime_error("direction_gradients_worker: packed CV_32F matrices of the picture's size expected");
@@ -302,7 +325,7 @@ public:
     static void shitomasi_corner_detection_worker(const cv::Mat& Jx, const cv::Mat& Jy, const cv::Mat& Jxy, const interval& iv, const float& /*k*/,
                                                   std::vector<std::vector<float>>& R_array) {
         const int rows = Jx.rows, cols = Jx.cols;
-        vofront::Context& c = vofront::default_context(rows, cols, 2000);
+        const vofront::DefaultCall c = vofront::default_call(rows, cols, 2000);
         vo_params p;
         vo_params_preset(&p, VO_PRESET_CPU_REF);
         p.threshold = RESPONSE_THRESHOLD;
@@ -313,10 +336,22 @@ public:
         for (int i = iv.rows.start + 2; i < iv.rows.end - 2; ++i)
             for (int j = iv.cols.start + 2; j < iv.cols.end - 2; ++j) R_array[i][j] = flat[(size_t)i * cols + j];
     }
-    // :166-208, keypoints in the order the manager hands them to FREAK (sorted by (y, x), feature_extraction_parallel.cpp:276-282)
+    // :166-208, keypoints in the reference's own order: it pops a max-heap of (R, i, j) tuples (:167,198-206), i.e.
+    // descending response, ties by descending row, then descending column - a caller that takes "the K strongest" from
+    // the front gets the reference's points.  The GPU returns the same SET sorted by (y, x) (what the manager sorts to
+    // next, feature_extraction_parallel.cpp:276-282); the heap order is restored here from the caller's own R_values.
     static std::vector<cv::KeyPoint> non_maximum_suppression(const std::vector<std::vector<float>>& R_values, const int& n_rows,
                                                              const int& n_cols, const int& k, const int& N) {
-        return vofront::non_maximum_suppression(vofront::default_context(n_rows, n_cols, N > 2000 ? N : 2000), R_values, n_rows, n_cols, k, N);
+        std::vector<cv::KeyPoint> kps =
+            vofront::non_maximum_suppression(vofront::default_call(n_rows, n_cols, N > 2000 ? N : 2000), R_values, n_rows, n_cols, k, N);
+        std::sort(kps.begin(), kps.end(), [&](const cv::KeyPoint& a, const cv::KeyPoint& b) {
+            const int ai = (int)a.pt.y, aj = (int)a.pt.x, bi = (int)b.pt.y, bj = (int)b.pt.x;
+            const float ra = R_values[ai][aj], rb = R_values[bi][bj];
+            if (ra != rb) return ra > rb;
+            if (ai != bi) return ai > bi;
+            return aj > bj;
+        });
+        return kps;
     }
 };
 
@@ -327,7 +362,7 @@ public:
     // FREAK_feature_descriptor_parallel.cpp:11-55
     static float compute_orientation(const cv::KeyPoint& point, const cv::Mat& image) {
         std::vector<float> ang;
-        vofront::FREAK_feature_description(vofront::default_context(image.rows, image.cols, 2000), {point}, image, &ang);
+        vofront::FREAK_feature_description(vofront::default_call(image.rows, image.cols, 2000), {point}, image, &ang);
         return ang.at(0);
     }
     // declared at .h:106 (its definition is commented out in the reference, .cpp:56-100: every keypoint, the start index unused)
@@ -343,7 +378,7 @@ public:
         if (hi <= starting_key_point_index) return;
         const std::vector<cv::KeyPoint> part(key_points.begin() + starting_key_point_index, key_points.begin() + hi);
         const int n = (int)part.size();
-        const auto d = vofront::FREAK_feature_description(vofront::default_context(blurred_gray_picture.rows, blurred_gray_picture.cols,
+        const auto d = vofront::FREAK_feature_description(vofront::default_call(blurred_gray_picture.rows, blurred_gray_picture.cols,
                                                                                    n > 2000 ? n : 2000), part, blurred_gray_picture);
         for (size_t q = 0; q < d.size(); ++q) descriptor[starting_key_point_index + q] = d[q];
     }

@@ -179,6 +179,9 @@ class Reference:
         lib.voref_response.argtypes = [_u8p, C.c_int, C.c_int, _f32p]
         lib.voref_nms.argtypes = [_f32p, C.c_int, C.c_int, C.c_int, C.c_int, _f32p]
         lib.voref_nms.restype = C.c_int
+        if hasattr(lib, "voref_nms_ranked"):
+            lib.voref_nms_ranked.argtypes = lib.voref_nms.argtypes
+            lib.voref_nms_ranked.restype = C.c_int
         lib.voref_orientation.argtypes = [_u8p, C.c_int, C.c_int, C.c_float, C.c_float]
         lib.voref_orientation.restype = C.c_float
         lib.voref_describe.argtypes = [_u8p, C.c_int, C.c_int, _f32p, C.c_int, _u8p]
@@ -232,6 +235,13 @@ class Reference:
         R = np.ascontiguousarray(R, np.float32)
         kp = np.empty((max(max_keypoints, 1), 2), np.float32)
         n = self.lib.voref_nms(R, R.shape[0], R.shape[1], nms_window, max_keypoints, kp)
+        return kp[:n].copy()
+
+    def nms_ranked(self, R, nms_window=5, max_keypoints=1500):
+        """The reference's own output order (heap order: descending (R, i, j)), before the manager's (y, x) sort."""
+        R = np.ascontiguousarray(R, np.float32)
+        kp = np.empty((max(max_keypoints, 1), 2), np.float32)
+        n = self.lib.voref_nms_ranked(R, R.shape[0], R.shape[1], nms_window, max_keypoints, kp)
         return kp[:n].copy()
 
     def orientation(self, blurred, x, y):

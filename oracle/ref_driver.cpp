@@ -152,6 +152,15 @@ int voref_nms(const float* R, int rows, int cols, int k, int N, float* kp_xy) {
     return static_cast<int>(kps.size());
 }
 
+// non_maximum_suppression(k, N) as the reference returns it: heap order, strongest first (corner_detection_parallel.cpp:198-206).
+int voref_nms_ranked(const float* R, int rows, int cols, int k, int N, float* kp_xy) {
+    std::vector<std::vector<float>> Rv(rows);
+    for (int i = 0; i < rows; ++i) Rv[i].assign(R + static_cast<size_t>(i) * cols, R + static_cast<size_t>(i + 1) * cols);
+    auto kps = CornerDetectionParallel::non_maximum_suppression(Rv, rows, cols, k, N);
+    for (size_t i = 0; i < kps.size(); ++i) { kp_xy[2 * i] = kps[i].pt.x; kp_xy[2 * i + 1] = kps[i].pt.y; }
+    return static_cast<int>(kps.size());
+}
+
 float voref_orientation(const uint8_t* blurred, int rows, int cols, float x, float y) {
     cv::Mat src(rows, cols, CV_8UC1, const_cast<uint8_t*>(blurred));
     return FREAK_Parallel::compute_orientation(cv::KeyPoint(cv::Point2f(x, y), 1.0f), src);

@@ -75,6 +75,15 @@ def unpack(packed):
     return np.ascontiguousarray(bits, np.uint8)
 
 
+def heap_order(kp_xy, R):
+    """Keypoints (x, y) in the order CornerDetectionParallel::non_maximum_suppression returns them: it pops a max-heap of
+    (R, i, j) tuples (corner_detection_parallel.cpp:167,198-206) = descending response, then row, then column."""
+    kp = np.asarray(kp_xy, np.float32).reshape(-1, 2)
+    x, y = kp[:, 0].astype(np.int64), kp[:, 1].astype(np.int64)
+    order = np.lexsort((-x, -y, -R[y, x].astype(np.float64)))
+    return kp[order]
+
+
 def dense_R(idx, val, shape):
     R = np.zeros(shape, np.float32)
     R.reshape(-1)[idx] = val

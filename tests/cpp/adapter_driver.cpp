@@ -6,6 +6,10 @@
 //   adapter_driver <in.raw> <out.bin>
 // in.raw : int32 rows, cols, then two gray u8 images of rows*cols bytes.
 // out.bin: for each of the sections below  int32 count  followed by the payload.
+#include <cstring>
+#include <thread>
+#include <atomic>
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include <fstream>
@@ -83,6 +87,14 @@ int main(int argc, char** argv) {
             CornerDetectionParallel::shitomasi_corner_detection_worker(Jx, Jy, Jxy, top, 0.05f, Rw);
             CornerDetectionParallel::shitomasi_corner_detection_worker(Jx, Jy, Jxy, bottom, 0.05f, Rw);
             auto kp2 = CornerDetectionParallel::non_maximum_suppression(Rw, rows, cols, 5, 1500);
+            // the facade's own order (the reference's heap order, strongest first), then the manager's sort
+            // (feature_extraction_parallel.cpp:276-282) before the descriptors
+            put_i32(out, (int32_t)kp2.size());
+            for (const auto& kq : kp2) { out.write(reinterpret_cast<const char*>(&kq.pt.x), 4); out.write(reinterpret_cast<const char*>(&kq.pt.y), 4); }
+            std::sort(kp2.begin(), kp2.end(), [](const cv::KeyPoint& a, const cv::KeyPoint& b) {
+                const int ay = static_cast<int>(a.pt.y), by = static_cast<int>(b.pt.y);
+                return ay == by ? static_cast<int>(a.pt.x) < static_cast<int>(b.pt.x) : ay < by;
+            });
             std::vector<std::vector<uint8_t>> d2(kp2.size(), std::vector<uint8_t>(512));
             for (size_t st = 0; st < kp2.size(); st += KEY_POINTS_PER_TASK)
                 FREAK_Parallel::FREAK_feature_description_worker(kp2, bl, st, d2, kp2.size());
@@ -117,6 +129,32 @@ int main(int argc, char** argv) {
             feature_extraction_manager_with_points(big, gpu_settings);
         } catch (const std::runtime_error&) { threw = 1; }
         put_i32(out, threw);
+        // --- 5. two threads through the context-less signatures with DIFFERENT image sizes: thread B's larger image makes
+        // the process-wide context grow while thread A is calling in.  Every result must equal the single-threaded one.
+        {
+            cv::Mat tall(rows + 40, cols, CV_8UC1);  // img2 with its last rows repeated: forces a regrowth
+            for (int i = 0; i < tall.rows; ++i) std::memcpy(tall.data + (size_t)i * tall.step, img2.data + (size_t)std::min(i, rows - 1) * img2.step, cols);
+            const auto want_a = feature_extraction_manager_with_points(bgr, pool1);
+            const auto want_b = feature_extraction_manager_with_points(tall, pool1);
+            const auto want_ma = matchCustomBinaryDescriptorsThreadPool(want_a.first, want_a.first, pool1, 4, 0.75f);
+            const auto want_mb = matchCustomBinaryDescriptorsThreadPool(want_b.first, want_a.first, pool1, 4, 0.75f);
+            std::atomic<int> bad{0};
+            auto worker = [&](bool b) {
+                try {
+                    thread_pool my_pool;
+                    for (int it = 0; it < 6; ++it) {
+                        const auto got = b ? feature_extraction_manager_with_points(tall, my_pool) : feature_extraction_manager_with_points(bgr, my_pool);
+                        const auto& want = b ? want_b : want_a;
+                        if (got.first != want.first || got.second.size() != want.second.size()) ++bad;
+                        if (matchCustomBinaryDescriptorsThreadPool(got.first, want_a.first, my_pool, 4, 0.75f) != (b ? want_mb : want_ma)) ++bad;
+                    }
+                } catch (const std::exception&) { bad += 100; }
+            };
+            std::thread ta(worker, false), tb(worker, true);
+            ta.join(); tb.join();
+            put_i32(out, (int32_t)want_b.second.size());
+            put_i32(out, bad.load());
+        }
     } catch (const std::exception& e) {
         std::cerr << "adapter_driver: " << e.what() << "\n";
         return 1;

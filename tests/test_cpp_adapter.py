@@ -76,6 +76,15 @@ def test_adapter_matches_oracle(tmp_path, oracle, factory):
     assert np.array_equal(kp, kp_o) and (d == d_o).mean() >= 0.9999
     # 3b. the reference's stage classes (CornerDetectionParallel / FREAK_Parallel statics), response computed in two
     # overlapping row intervals: the same keypoints and descriptors again
+    # ... and the facade's own output order is the reference's: strongest first (heap of (R, i, j),
+    # corner_detection_parallel.cpp:198-206; the rule is pinned to the reference's code in tests/test_oracle.py)
+    from conftest import heap_order
+    (n_ranked,) = struct.unpack_from("<i", buf, off)
+    ranked = np.frombuffer(buf, np.float32, 2 * n_ranked, off + 4).reshape(n_ranked, 2)
+    off += 4 + 8 * n_ranked
+    R_o = oracle.response(oracle.blur(f1), 25000.0)
+    assert n_ranked == len(kp_o) and np.array_equal(ranked, heap_order(kp_o, R_o))
+    assert not np.array_equal(ranked, kp_o)
     kp, d, off = _read_features(buf, off)
     assert np.array_equal(kp, kp_o) and (d == d_o).mean() >= 0.9999
     (npx,) = struct.unpack_from("<i", buf, off)
@@ -100,4 +109,9 @@ def test_adapter_matches_oracle(tmp_path, oracle, factory):
     assert np.array_equal(m_edit, oracle.match(d1e, d2, 32, 0.75))
     # 4. empty input -> empty result; oversize image -> std::runtime_error
     n_empty, threw = struct.unpack_from("<ii", buf, off)
+    off += 8
     assert n_empty == 0 and threw == 1
+    # 5. two threads with different image sizes through the context-less signatures (one makes the process-wide context
+    # grow while the other is calling in): all 12 extractions and matches equal the single-threaded results
+    n_tall, bad = struct.unpack_from("<ii", buf, off)
+    assert n_tall > 0 and bad == 0

@@ -175,3 +175,28 @@ def test_split_weight_product_is_exact(oracle):
     Exhaustive proof over the whole input domain (903 pairs x 511 intensity differences x 2 axes)."""
     bad, total = oracle.check_split_weight()
     assert total == 903 * 511 * 2 and bad == 0
+
+
+
+def test_heap_order_rule_equals_the_references_own_output_order(oracle, reference, factory):
+    """The reference's non_maximum_suppression returns keypoints as its max-heap of (R, i, j) pops them.  The adapter's
+    CornerDetectionParallel::non_maximum_suppression facade restores that order from the (y, x)-sorted GPU list; the
+    rule it uses (tests/conftest.py::heap_order) is pinned here to the reference's own code, on the factory response map
+    and on a map with equal responses (ties go to the larger row, then the larger column)."""
+    from conftest import heap_order
+    if not hasattr(reference.lib, "voref_nms_ranked"):
+        pytest.skip("oracle/_ref/libvoref.so predates voref_nms_ranked: rebuild it with /root/reference present")
+    R = oracle.response(oracle.blur(factory[0]), 25000.0)
+    for window, n in ((5, 1500), (3, 2000), (5, 40)):
+        ranked = reference.nms_ranked(R, window, n)
+        assert len(ranked) == len(reference.nms(R, window, n)) > 0
+        assert np.array_equal(ranked, heap_order(reference.nms(R, window, n), R)), (window, n)
+        assert np.array_equal(ranked, heap_order(oracle.nms(R, window, n), R)), (window, n)
+        assert (np.diff(R[ranked[:, 1].astype(int), ranked[:, 0].astype(int)]) <= 0).all()      # strongest first
+    T = np.zeros((120, 160), np.float32)
+    for (i, j) in ((40, 50), (40, 90), (70, 50), (70, 120), (50, 70)):
+        T[i, j] = 30000.0
+    T[60, 100] = 40000.0
+    ranked = reference.nms_ranked(T, 5, 10)
+    assert ranked.tolist() == [[100, 60], [120, 70], [50, 70], [70, 50], [90, 40], [50, 40]]
+    assert np.array_equal(ranked, heap_order(oracle.nms(T, 5, 10), T))
